@@ -1,0 +1,162 @@
+/* include/gs2d.h — C ABI of the B200-native 2D Gaussian-splatting image-fitting engine.
+ *
+ * The reference (Ushio/2dGaussianSplatting) has no plugin/FFI boundary: its optimisation step is the body of
+ * `while( pr::NextFrame() == false )` in main() (main.cpp:334, hot part main.cpp:414-809) operating on locals.
+ * This header therefore puts the boundary at the DATA CONTRACT of that loop body: the AoS types below are
+ * byte-identical to the reference's `Splat` (main.cpp:85-93) and `SplatAdam` (main.cpp:158-166); the target and
+ * the rendered image are row-major RGBA float32 exactly like `pr::Image2DRGBA32` (prp.cpp:347-352, 751-756).
+ * A patched main.cpp-style driver calls gs2d_step() in place of lines 414-809.
+ *
+ * Conventions
+ *   - every function returns GS2D_OK (0) or a negative GS2D_ERR_* code; nothing aborts or throws across the ABI
+ *   - the caller owns every host pointer; the library copies (through its own pinned staging)
+ *   - a context is driven by ONE host thread (mirrors the reference); distinct contexts are independent
+ *   - there is NO CPU fallback: gs2d_create fails with GS2D_ERR_NO_DEVICE unless an sm_100 device is present
+ *   - "image" arguments index independent fitting problems (BASELINE config 5); pass 0 for a single image
+ */
+#ifndef GS2D_H
+#define GS2D_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS2D_VERSION 100
+
+enum
+{
+	GS2D_OK = 0,
+	GS2D_ERR_INVALID = -1,   /* bad argument */
+	GS2D_ERR_NO_DEVICE = -2, /* no sm_100 CUDA device / driver */
+	GS2D_ERR_CUDA = -3,      /* a CUDA call failed; gs2d_last_error() has the text */
+	GS2D_ERR_NONFINITE = -4, /* non-aborting mirror of main.cpp:752-785 (colour, sx, sy, rot or pos.x not finite) */
+	GS2D_ERR_OOM = -5,       /* device or pinned allocation failed */
+	GS2D_ERR_NCCL = -6,      /* NCCL missing or a collective failed */
+	GS2D_ERR_STATE = -7      /* call sequence error (e.g. backward before forward) */
+};
+
+/* == struct Splat, 36 bytes (main.cpp:85-93); also the layout of dSplats (main.cpp:550) */
+typedef struct gs2d_splat
+{
+	float pos[2];
+	float sx, sy;
+	float rot;
+	float color[3];
+	float opacity;
+} gs2d_splat;
+
+/* == struct Adam (main.cpp:139-143) */
+typedef struct gs2d_moment
+{
+	float m, v;
+} gs2d_moment;
+
+/* == struct SplatAdam, 72 bytes (main.cpp:158-166) */
+typedef struct gs2d_splat_adam
+{
+	gs2d_moment pos[2];
+	gs2d_moment sx, sy;
+	gs2d_moment rot;
+	gs2d_moment color[3];
+	gs2d_moment opacity;
+} gs2d_splat_adam;
+
+/* Every literal of the reference's loop body, defaulting to the reference's values (gs2d_default_params). */
+typedef struct gs2d_params
+{
+	float lr;               /* 0.05   main.cpp:715 */
+	float beta1, beta2;     /* .9 .99 main.cpp:136-137 */
+	float eps;              /* 1e-15  main.cpp:154 */
+	float bounds;           /* 3.0    main.cpp:7   (only 3.0 is supported by the CUDA path) */
+	float min_throughput;   /* 1/256  main.cpp:8 */
+	float s_min, s_max;     /* 1,1024 main.cpp:744-745 */
+	float o_min, o_max;     /* .1, 1  main.cpp:749 */
+	int optimize_opacity;   /* 0      main.cpp:317 */
+} gs2d_params;
+
+/* Per-iteration work counters (device-side counts, for the roofline). */
+typedef struct gs2d_stats
+{
+	uint64_t keys;          /* (tile, splat) list entries binned this iteration */
+	uint64_t live_pairs;    /* (pixel, splat) pairs blended with T >= min_throughput, forward pass */
+	uint64_t staged;        /* list entries actually staged by the forward kernel before tile termination */
+	uint64_t capacity;      /* current capacity of the key buffers (entries) */
+} gs2d_stats;
+
+typedef struct gs2d_ctx gs2d_ctx;
+
+void gs2d_default_params( gs2d_params* p );
+int gs2d_version( void );
+const char* gs2d_strerror( int code );
+const char* gs2d_last_error( const gs2d_ctx* ctx ); /* text of the last CUDA/NCCL failure ("" if none) */
+
+/* Create a context on CUDA device `device` for `n_images` independent W x H problems with n_splats Gaussians each.
+ * params == NULL selects gs2d_default_params. */
+int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_images, int device, const gs2d_params* params );
+void gs2d_destroy( gs2d_ctx* ctx );
+
+/* Target = imageRef (main.cpp:254-258): H*W*4 floats, row-major RGBA, A ignored. */
+int gs2d_set_target_rgba32f( gs2d_ctx* ctx, int image, const float* rgba );
+/* Target from 8-bit RGBA as decoded by stb (prp.cpp:185): converted on device as u8/255.0f (prp.cpp:796-807). */
+int gs2d_set_target_rgba8( gs2d_ctx* ctx, int image, const uint8_t* rgba );
+
+/* init() of the reference (main.cpp:280-305) evaluated on the device for every image; resets Adam moments,
+ * beta powers and the iteration counter ("Restart" button, main.cpp:828-831). */
+int gs2d_init_reference( gs2d_ctx* ctx );
+
+/* Checkpoint format == the reference's loop-carried state (main.cpp:271-278). adam may be NULL (zeros) on upload
+ * and NULL (skipped) on download; scalars may be NULL on download. */
+int gs2d_upload_state( gs2d_ctx* ctx, int image, const gs2d_splat* splats, const gs2d_splat_adam* adam, float beta1t,
+                       float beta2t, int iteration );
+int gs2d_download_state( gs2d_ctx* ctx, int image, gs2d_splat* splats, gs2d_splat_adam* adam, float* beta1t,
+                         float* beta2t, int* iteration );
+
+int gs2d_set_optimize_opacity( gs2d_ctx* ctx, int enabled ); /* the ImGui checkbox, main.cpp:825 */
+
+/* n_iters full iterations (bin+sort, forward, backward, [allreduce], Adam), main.cpp:414-809.
+ * mse: NULL => enqueue only (asynchronous); else n_iters*n_images doubles, mse[it*n_images+img] = the value the
+ * reference prints at main.cpp:807 (render made with the pre-update parameters), and the call blocks. */
+int gs2d_step( gs2d_ctx* ctx, int n_iters, double* mse );
+
+/* The three phases separately, for parity tests. forward = bin + sort + blend + loss (main.cpp:414-546, 796-805);
+ * backward = main.cpp:548-712 (always includes d/d opacity); adam = main.cpp:714-785. */
+int gs2d_forward( gs2d_ctx* ctx );
+int gs2d_backward( gs2d_ctx* ctx );
+int gs2d_adam( gs2d_ctx* ctx );
+
+int gs2d_download_image_rgba32f( gs2d_ctx* ctx, int image, float* rgba ); /* image0 with w == 1 (main.cpp:788-792) */
+int gs2d_download_grads( gs2d_ctx* ctx, int image, gs2d_splat* dsplats );  /* == dSplats (main.cpp:550) */
+int gs2d_last_mse( gs2d_ctx* ctx, double* mse /* n_images */ );            /* loss of the last forward */
+int gs2d_get_stats( gs2d_ctx* ctx, gs2d_stats* out );                      /* counters of the last forward */
+
+/* Tile-row band sharding across ranks (BASELINE config 3/4): this context renders and back-propagates only tile
+ * rows [rank*ceil(R/n), ...) of every image; gradients and the loss are summed over ranks before Adam.
+ * gs2d_comm_unique_id fills a 128-byte NCCL id on rank 0; the caller ships it to the other ranks (any transport)
+ * and every rank calls gs2d_comm_init. One process per GPU. */
+int gs2d_comm_unique_id( uint8_t id[128] );
+int gs2d_comm_init( gs2d_ctx* ctx, int rank, int n_ranks, const uint8_t id[128] );
+/* Band sharding WITHOUT a communicator (host-side tests on one GPU: render bands separately and add them up). */
+int gs2d_set_band( gs2d_ctx* ctx, int rank, int n_ranks );
+
+/* Device time of the last completed gs2d_step call, milliseconds, CUDA events on the context's stream. */
+int gs2d_last_step_ms( gs2d_ctx* ctx, float* ms );
+/* Per-kernel-group device times of one extra profiled iteration (does advance the fit by one iteration):
+ * out[0]=preprocess+scan+emit, [1]=sort, [2]=forward, [3]=backward, [4]=allreduce, [5]=adam+finalise. */
+int gs2d_profile_step( gs2d_ctx* ctx, float out_ms[6] );
+/* Number of kernel launches the library has issued on this context so far. */
+int gs2d_launch_count( gs2d_ctx* ctx, uint64_t* n );
+
+int gs2d_sync( gs2d_ctx* ctx );
+
+/* Microbenchmarks that give the roofline denominators on the device at hand:
+ * FP32 FMA issue rate (TFLOP/s, FMA = 2 flop) and HBM copy bandwidth (GB/s, read+write bytes). */
+int gs2d_microbench_fp32( int device, double* tflops );
+int gs2d_microbench_hbm( int device, double* gbs );
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS2D_H */
