@@ -1,0 +1,302 @@
+// gs2d_adam.cu — loss finalisation, Adam + clamps (main.cpp:714-785), reference init (main.cpp:280-305) and the
+// AoS <-> SoA conversions at the ABI.
+#include "gs2d_internal.cuh"
+
+// glm::clamp = min( max( x, lo ), hi ) with comparison-based min/max (func_common.inl:17-30): NaN survives.
+__device__ __forceinline__ float clamp_glm( float x, float lo, float hi )
+{
+	float t = ( x < lo ) ? lo : x;
+	return ( hi < t ) ? hi : t;
+}
+
+// ------------------------------------------------------------------------------------------------------ loss ---
+// One block per image: deterministic sum of the per-tile partials of this rank's band (double).
+__global__ void __launch_bounds__( 256 ) k_finalize_loss( Geometry g, const double* __restrict__ loss_partial,
+                                                          double* __restrict__ loss,
+                                                          const unsigned long long* __restrict__ slots,
+                                                          unsigned long long* __restrict__ stats,
+                                                          const DevState* __restrict__ st )
+{
+	__shared__ double red[256];
+	const int img = blockIdx.x;
+	const int t0 = ( img * g.tiles_y + g.band_ty0 ) * g.tiles_x;
+	const int t1 = ( img * g.tiles_y + g.band_ty1 ) * g.tiles_x;
+	double s = 0.0;
+	for( int t = t0 + threadIdx.x; t < t1; t += 256 )
+		s += loss_partial[t];
+	red[threadIdx.x] = s;
+	__syncthreads();
+	for( int o = 128; o > 0; o >>= 1 )
+	{
+		if( threadIdx.x < o )
+			red[threadIdx.x] += red[threadIdx.x + o];
+		__syncthreads();
+	}
+	if( threadIdx.x == 0 )
+		loss[img] = red[0];
+	// overflow vote: summed over ranks together with the loss, so that every rank skips the same iterations
+	if( img == 0 && threadIdx.x == 0 )
+		loss[g.n_images] = st->need_capacity ? 1.0 : 0.0;
+	if( img == 0 && threadIdx.x < 2 )
+	{
+		unsigned long long a = 0;
+		for( int i = 0; i < GS2D_LIVE_SLOTS; i++ )
+			a += slots[threadIdx.x * GS2D_LIVE_SLOTS + i];
+		stats[threadIdx.x] = a;
+	}
+}
+
+// One thread block: publish the mse values (main.cpp:805-807), advance beta powers (main.cpp:718-719) and the
+// iteration counter (main.cpp:809). Runs after the (all-reduced) loss is final and before k_adam.
+__global__ void k_advance( Geometry g, const double* __restrict__ loss, double* __restrict__ mse_ring, int mse_cap,
+                           float beta1, float beta2, DevState* st )
+{
+	if( loss[g.n_images] != 0.0 )
+		return; // some rank ran out of key capacity: the iteration is void everywhere (redone by the host)
+	const int slot = st->mse_slot;
+	for( int i = threadIdx.x; i < g.n_images; i += blockDim.x )
+		if( slot < mse_cap )
+			mse_ring[(size_t)slot * g.n_images + i] = loss[i] / (double)( g.H * g.W * 3 );
+	__syncthreads();
+	if( threadIdx.x == 0 )
+	{
+		st->mse_slot = slot + 1;
+		st->beta1t = xmul( st->beta1t, beta1 );
+		st->beta2t = xmul( st->beta2t, beta2 );
+		st->iteration += 1;
+	}
+}
+
+// ------------------------------------------------------------------------------------------------------ Adam ---
+// Adam::optimize, main.cpp:144-156 — reference operand order, IEEE division and square root, no contraction.
+__device__ __forceinline__ float adam_one( float value, float gr, float& m_io, float& v_io, float lr, float beta1,
+                                           float beta2, float eps, float om_b1t, float om_b2t )
+{
+	const float m = xadd( xmul( beta1, m_io ), xmul( xsub( 1.0f, beta1 ), gr ) );
+	const float v = xadd( xmul( beta2, v_io ), xmul( xmul( xsub( 1.0f, beta2 ), gr ), gr ) );
+	m_io = m;
+	v_io = v;
+	const float m_hat = xdiv( m, om_b1t );
+	const float v_hat = xdiv( v, om_b2t );
+	return xsub( value, xdiv( xmul( lr, m_hat ), xadd( xsqrt( v_hat ), eps ) ) );
+}
+
+// One thread per 4 consecutive splats, 128-bit accesses on every SoA plane: reads p, g, m, v, writes p, m, v and
+// zeroes g for the next iteration (28 + 4 bytes per scalar; HBM-bound).
+__global__ void __launch_bounds__( 256 ) k_adam( Geometry g, float* __restrict__ params, float* __restrict__ grads,
+                                                 float* __restrict__ adam_m, float* __restrict__ adam_v,
+                                                 gs2d_params hp, const double* __restrict__ loss, DevState* st )
+{
+	if( loss[g.n_images] != 0.0 )
+		return;
+	const int i4 = ( blockIdx.x * 256 + threadIdx.x ) * 4;
+	if( i4 >= g.n_total )
+		return;
+	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
+	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
+	bool bad = false;
+	// update order of the reference: colour, pos, sx, sy, rot, opacity (main.cpp:723-738) — independent scalars
+#pragma unroll
+	for( int pl = 0; pl < GS2D_NPLANES; pl++ )
+	{
+		const size_t o = (size_t)pl * g.n_pad + i4;
+		float4 p = *reinterpret_cast<float4*>( params + o );
+		float4 gr = *reinterpret_cast<float4*>( grads + o );
+		float pv[4] = { p.x, p.y, p.z, p.w }, gv[4] = { gr.x, gr.y, gr.z, gr.w };
+		if( pl != PL_OP || hp.optimize_opacity )
+		{
+			float4 m = *reinterpret_cast<float4*>( adam_m + o );
+			float4 v = *reinterpret_cast<float4*>( adam_v + o );
+			float mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+			for( int k = 0; k < 4; k++ )
+				pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
+			*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
+			*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
+		}
+		// constraints, main.cpp:740-749
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+		{
+			float x = pv[k];
+			if( pl == PL_PX )
+				x = clamp_glm( x, 0.0f, wmax );
+			else if( pl == PL_PY )
+				x = clamp_glm( x, 0.0f, hmax );
+			else if( pl == PL_SX || pl == PL_SY )
+				x = clamp_glm( x, hp.s_min, hp.s_max );
+			else if( pl == PL_CR || pl == PL_CG || pl == PL_CB )
+				x = clamp_glm( x, 0.0f, 1.0f );
+			else if( pl == PL_OP )
+				x = clamp_glm( x, hp.o_min, hp.o_max );
+			pv[k] = x;
+			// finite check, main.cpp:752-785: colour, sx, sy, rot, pos.x (pos.y and opacity are not checked)
+			if( pl != PL_PY && pl != PL_OP && i4 + k < g.n_total && !isfinite( x ) )
+				bad = true;
+		}
+		*reinterpret_cast<float4*>( params + o ) = make_float4( pv[0], pv[1], pv[2], pv[3] );
+		*reinterpret_cast<float4*>( grads + o ) = make_float4( 0.f, 0.f, 0.f, 0.f );
+	}
+	if( bad )
+		atomicOr( &st->nonfinite, 1 );
+}
+
+// ------------------------------------------------------------------------------------------------------ init ---
+__device__ __forceinline__ void pcg3d( unsigned& x, unsigned& y, unsigned& z ) // main.cpp:17-24
+{
+	x = x * 1664525u + 1013904223u;
+	y = y * 1664525u + 1013904223u;
+	z = z * 1664525u + 1013904223u;
+	x += y * z;
+	y += z * x;
+	z += x * y;
+	x ^= x >> 16u;
+	y ^= y >> 16u;
+	z ^= z >> 16u;
+	x += y * z;
+	y += z * x;
+	z += x * y;
+}
+__device__ __forceinline__ float mix_glm( float x, float y, float a ) // x*(1-a) + y*a, func_common.inl:123-133
+{
+	return xadd( xmul( x, xsub( 1.0f, a ) ), xmul( y, a ) );
+}
+
+__global__ void __launch_bounds__( 256 ) k_init_reference( Geometry g, float* __restrict__ params )
+{
+	const int gi = blockIdx.x * 256 + threadIdx.x;
+	if( gi >= g.n_total )
+		return;
+	const unsigned i = (unsigned)( gi % g.n_splats );
+	unsigned ax = i, ay = 0u, az = 0xFFFFFFFFu, bx = i, by = 1u, bz = 0xFFFFFFFFu;
+	pcg3d( ax, ay, az );
+	pcg3d( bx, by, bz );
+	const float denom = 4294967296.0f; // (float)0xFFFFFFFF, main.cpp:290-291
+	const float r0x = xdiv( __uint2float_rn( ax ), denom ), r0y = xdiv( __uint2float_rn( ay ), denom );
+	const float r1x = xdiv( __uint2float_rn( bx ), denom ), r1y = xdiv( __uint2float_rn( by ), denom ),
+	            r1z = xdiv( __uint2float_rn( bz ), denom );
+	params[PL_PX * g.n_pad + gi] = mix_glm( r0x, xsub( (float)g.W, 1.0f ), r0x );
+	params[PL_PY * g.n_pad + gi] = mix_glm( r0y, xsub( (float)g.H, 1.0f ), r0y );
+	params[PL_SX * g.n_pad + gi] = mix_glm( 6.0f, 10.0f, r1x );
+	params[PL_SY * g.n_pad + gi] = mix_glm( 6.0f, 10.0f, r1y );
+	params[PL_ROT * g.n_pad + gi] = xmul( 3.14159265358979323846264338327950288f, r1z );
+	params[PL_CR * g.n_pad + gi] = 0.5f;
+	params[PL_CG * g.n_pad + gi] = 0.5f;
+	params[PL_CB * g.n_pad + gi] = 0.5f;
+	params[PL_OP * g.n_pad + gi] = 1.0f;
+}
+
+// Image2DRGBA8_to_Image2DRGBA32: vec4( u8 ) / vec4( 255.0f ), prp.cpp:796-807
+__global__ void __launch_bounds__( 256 ) k_u8_to_target( const uchar4* __restrict__ src, float4* __restrict__ dst,
+                                                         size_t n )
+{
+	const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+	if( i >= n )
+		return;
+	const uchar4 c = src[i];
+	dst[i] = make_float4( xdiv( (float)c.x, 255.0f ), xdiv( (float)c.y, 255.0f ), xdiv( (float)c.z, 255.0f ),
+	                      xdiv( (float)c.w, 255.0f ) );
+}
+
+// ------------------------------------------------------------------------------------------- AoS <-> SoA -------
+// Splat field f (0..8) <-> plane f; SplatAdam stores {m,v} pairs in the same field order (main.cpp:158-166).
+__global__ void __launch_bounds__( 256 ) k_aos_to_soa( Geometry g, int image, const float* __restrict__ splats,
+                                                       const float* __restrict__ adam, float* __restrict__ params,
+                                                       float* __restrict__ adam_m, float* __restrict__ adam_v )
+{
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	if( i >= g.n_splats )
+		return;
+	const size_t gi = (size_t)image * g.n_splats + i;
+#pragma unroll
+	for( int f = 0; f < GS2D_NPLANES; f++ )
+	{
+		params[(size_t)f * g.n_pad + gi] = splats[(size_t)i * 9 + f];
+		adam_m[(size_t)f * g.n_pad + gi] = adam ? adam[(size_t)i * 18 + 2 * f] : 0.0f;
+		adam_v[(size_t)f * g.n_pad + gi] = adam ? adam[(size_t)i * 18 + 2 * f + 1] : 0.0f;
+	}
+}
+__global__ void __launch_bounds__( 256 ) k_soa_to_aos( Geometry g, int image, float* __restrict__ splats,
+                                                       float* __restrict__ adam, float* __restrict__ gsplats,
+                                                       const float* __restrict__ params,
+                                                       const float* __restrict__ adam_m,
+                                                       const float* __restrict__ adam_v,
+                                                       const float* __restrict__ grads )
+{
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	if( i >= g.n_splats )
+		return;
+	const size_t gi = (size_t)image * g.n_splats + i;
+#pragma unroll
+	for( int f = 0; f < GS2D_NPLANES; f++ )
+	{
+		if( splats )
+			splats[(size_t)i * 9 + f] = params[(size_t)f * g.n_pad + gi];
+		if( adam )
+		{
+			adam[(size_t)i * 18 + 2 * f] = adam_m[(size_t)f * g.n_pad + gi];
+			adam[(size_t)i * 18 + 2 * f + 1] = adam_v[(size_t)f * g.n_pad + gi];
+		}
+		if( gsplats )
+			gsplats[(size_t)i * 9 + f] = grads[(size_t)f * g.n_pad + gi];
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------- launch ---
+int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s )
+{
+	const size_t plane_bytes = sizeof( float ) * (size_t)g.n_pad * GS2D_NPLANES;
+	cudaMemsetAsync( b.params, 0, plane_bytes, s );
+	cudaMemsetAsync( b.grads, 0, plane_bytes, s );
+	cudaMemsetAsync( b.adam_m, 0, plane_bytes, s );
+	cudaMemsetAsync( b.adam_v, 0, plane_bytes, s );
+	if( g.n_total == 0 )
+		return 0;
+	k_init_reference<<<( g.n_total + 255 ) / 256, 256, 0, s>>>( g, b.params );
+	return 1;
+}
+int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s )
+{
+	k_u8_to_target<<<(unsigned)( ( n_px + 255 ) / 256 ), 256, 0, s>>>( reinterpret_cast<const uchar4*>( src_dev ), dst,
+	                                                                   n_px );
+	return 1;
+}
+int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s )
+{
+	k_finalize_loss<<<g.n_images, 256, 0, s>>>( g, b.loss_partial, b.loss, b.live_slots, b.stats, b.state );
+	return 1;
+}
+int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s )
+{
+	k_advance<<<1, 256, 0, s>>>( g, b.loss, b.mse_ring, b.mse_cap, p.beta1, p.beta2, b.state );
+	return 1;
+}
+int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s )
+{
+	if( g.n_total == 0 )
+		return 0;
+	const int n4 = ( g.n_total + 3 ) / 4;
+	k_adam<<<( n4 + 255 ) / 256, 256, 0, s>>>( g, b.params, b.grads, b.adam_m, b.adam_v, p, b.loss, b.state );
+	return 1;
+}
+int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,
+                       const gs2d_splat_adam* adam_dev, cudaStream_t s )
+{
+	if( g.n_splats == 0 )
+		return 0;
+	k_aos_to_soa<<<( g.n_splats + 255 ) / 256, 256, 0, s>>>( g, image, reinterpret_cast<const float*>( splats_dev ),
+	                                                         reinterpret_cast<const float*>( adam_dev ), b.params,
+	                                                         b.adam_m, b.adam_v );
+	return 1;
+}
+int launch_soa_to_aos( const Geometry& g, const Buffers& b, int image, gs2d_splat* splats_dev,
+                       gs2d_splat_adam* adam_dev, gs2d_splat* grads_dev, cudaStream_t s )
+{
+	if( g.n_splats == 0 )
+		return 0;
+	k_soa_to_aos<<<( g.n_splats + 255 ) / 256, 256, 0, s>>>( g, image, reinterpret_cast<float*>( splats_dev ),
+	                                                         reinterpret_cast<float*>( adam_dev ),
+	                                                         reinterpret_cast<float*>( grads_dev ), b.params, b.adam_m,
+	                                                         b.adam_v, b.grads );
+	return 1;
+}

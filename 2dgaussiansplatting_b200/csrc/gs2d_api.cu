@@ -1,0 +1,844 @@
+// gs2d_api.cu — host side of the C ABI (include/gs2d.h): context, device memory, the per-iteration launch sequence,
+// state upload/download in the reference's AoS layouts, NCCL (dlopen'ed) for band-sharded multi-GPU fits.
+//
+// There is no CPU implementation of anything here: without an sm_100 device gs2d_create fails.
+#include "gs2d_internal.cuh"
+
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+// ---- minimal NCCL surface, resolved at run time (only needed when gs2d_comm_init is called) --------------------
+typedef struct ncclComm* ncclComm_t;
+typedef struct
+{
+	char internal[128];
+} ncclUniqueId_;
+struct NcclApi
+{
+	void* handle = nullptr;
+	int ( *GetUniqueId )( ncclUniqueId_* ) = nullptr;
+	int ( *CommInitRank )( ncclComm_t*, int, ncclUniqueId_, int ) = nullptr;
+	int ( *CommDestroy )( ncclComm_t ) = nullptr;
+	int ( *AllReduce )( const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t ) = nullptr;
+	int ( *GroupStart )() = nullptr;
+	int ( *GroupEnd )() = nullptr;
+	const char* ( *GetErrorString )( int ) = nullptr;
+};
+static NcclApi g_nccl;
+static bool nccl_load()
+{
+	if( g_nccl.handle )
+		return true;
+	const char* names[] = { "libnccl.so.2", "libnccl.so" };
+	void* h = nullptr;
+	for( const char* n : names )
+		if( ( h = dlopen( n, RTLD_NOW | RTLD_GLOBAL ) ) )
+			break;
+	if( !h )
+		return false;
+	g_nccl.GetUniqueId = (int ( * )( ncclUniqueId_* ))dlsym( h, "ncclGetUniqueId" );
+	g_nccl.CommInitRank = (int ( * )( ncclComm_t*, int, ncclUniqueId_, int ))dlsym( h, "ncclCommInitRank" );
+	g_nccl.CommDestroy = (int ( * )( ncclComm_t ))dlsym( h, "ncclCommDestroy" );
+	g_nccl.AllReduce =
+	    (int ( * )( const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t ))dlsym( h, "ncclAllReduce" );
+	g_nccl.GroupStart = (int ( * )())dlsym( h, "ncclGroupStart" );
+	g_nccl.GroupEnd = (int ( * )())dlsym( h, "ncclGroupEnd" );
+	g_nccl.GetErrorString = (const char* ( * )( int ))dlsym( h, "ncclGetErrorString" );
+	if( !g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy )
+		return false;
+	g_nccl.handle = h;
+	return true;
+}
+enum
+{
+	NCCL_FLOAT32 = 7,
+	NCCL_FLOAT64 = 8,
+	NCCL_SUM = 0
+};
+
+// ---- context ----------------------------------------------------------------------------------------------------
+struct gs2d_ctx
+{
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	Geometry g{};
+	Buffers b{};
+	gs2d_params hp{};
+	int sorted_buf = 0;
+	bool have_forward = false;
+	uint64_t launches = 0;
+	char err[512] = { 0 };
+
+	void* pinned = nullptr; // host staging
+	size_t pinned_bytes = 0;
+	void* dstage = nullptr; // device staging (AoS <-> SoA, u8 targets)
+	size_t dstage_bytes = 0;
+	DevState* h_state = nullptr; // pinned mirror
+
+	long long expected_iteration = 0; // what the device counter will read once everything enqueued has run
+	cudaEvent_t ev[10]{};
+	float last_ms = 0.0f;
+
+	ncclComm_t comm = nullptr;
+	int rank = 0, n_ranks = 1;
+};
+
+#define CK( call )                                                                                                    \
+	do                                                                                                                \
+	{                                                                                                                 \
+		cudaError_t e_ = ( call );                                                                                    \
+		if( e_ != cudaSuccess )                                                                                       \
+		{                                                                                                             \
+			snprintf( c->err, sizeof( c->err ), "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString( e_ ) ); \
+			return ( e_ == cudaErrorMemoryAllocation ) ? GS2D_ERR_OOM : GS2D_ERR_CUDA;                                \
+		}                                                                                                             \
+	} while( 0 )
+
+static int check_launch( gs2d_ctx* c )
+{
+	cudaError_t e = cudaGetLastError();
+	if( e != cudaSuccess )
+	{
+		snprintf( c->err, sizeof( c->err ), "kernel launch failed: %s", cudaGetErrorString( e ) );
+		return GS2D_ERR_CUDA;
+	}
+	return GS2D_OK;
+}
+
+extern "C" void gs2d_default_params( gs2d_params* p )
+{
+	p->lr = 0.05f;
+	p->beta1 = 0.9f;
+	p->beta2 = 0.99f;
+	p->eps = 1.0e-15f;
+	p->bounds = 3.0f;
+	p->min_throughput = 1.0f / 256.0f;
+	p->s_min = 1.0f;
+	p->s_max = 1024.0f;
+	p->o_min = 0.1f;
+	p->o_max = 1.0f;
+	p->optimize_opacity = 0;
+}
+extern "C" int gs2d_version( void ) { return GS2D_VERSION; }
+extern "C" const char* gs2d_strerror( int code )
+{
+	switch( code )
+	{
+	case GS2D_OK: return "ok";
+	case GS2D_ERR_INVALID: return "invalid argument";
+	case GS2D_ERR_NO_DEVICE: return "no sm_100 CUDA device available (there is no CPU fallback)";
+	case GS2D_ERR_CUDA: return "CUDA error";
+	case GS2D_ERR_NONFINITE: return "non-finite splat parameter (the reference would abort here, main.cpp:752-785)";
+	case GS2D_ERR_OOM: return "out of memory";
+	case GS2D_ERR_NCCL: return "NCCL unavailable or failed";
+	case GS2D_ERR_STATE: return "call sequence error";
+	default: return "unknown error";
+	}
+}
+extern "C" const char* gs2d_last_error( const gs2d_ctx* c ) { return c ? c->err : ""; }
+
+static int ensure_staging( gs2d_ctx* c, size_t bytes )
+{
+	if( bytes > c->pinned_bytes )
+	{
+		if( c->pinned )
+			cudaFreeHost( c->pinned );
+		c->pinned = nullptr;
+		c->pinned_bytes = 0;
+		CK( cudaMallocHost( &c->pinned, bytes ) );
+		c->pinned_bytes = bytes;
+	}
+	if( bytes > c->dstage_bytes )
+	{
+		if( c->dstage )
+			cudaFree( c->dstage );
+		c->dstage = nullptr;
+		c->dstage_bytes = 0;
+		CK( cudaMalloc( &c->dstage, bytes ) );
+		c->dstage_bytes = bytes;
+	}
+	return GS2D_OK;
+}
+
+static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
+{
+	Buffers& b = c->b;
+	for( int i = 0; i < 2; i++ )
+	{
+		if( b.keys[i] )
+			cudaFree( b.keys[i] );
+		if( b.vals[i] )
+			cudaFree( b.vals[i] );
+		b.keys[i] = b.vals[i] = nullptr;
+	}
+	if( b.radix_hist )
+		cudaFree( b.radix_hist );
+	b.radix_hist = nullptr;
+	capacity = std::min<unsigned long long>( std::max<unsigned long long>( capacity, 1ull << 16 ), 0xFFFF0000ull );
+	for( int i = 0; i < 2; i++ )
+	{
+		CK( cudaMalloc( &b.keys[i], sizeof( unsigned ) * capacity ) );
+		CK( cudaMalloc( &b.vals[i], sizeof( unsigned ) * capacity ) );
+	}
+	b.capacity = capacity;
+	b.max_chunks = (unsigned)( ( capacity + 4095 ) / 4096 );
+	const size_t hist_n = 256ull * b.max_chunks;
+	CK( cudaMalloc( &b.radix_hist, sizeof( unsigned ) * ( hist_n + hist_n / 1024 + 16 ) ) );
+	return GS2D_OK;
+}
+
+static void set_band( gs2d_ctx* c, int rank, int n_ranks )
+{
+	const int per = ( c->g.tiles_y + n_ranks - 1 ) / n_ranks;
+	c->g.band_ty0 = std::min( rank * per, c->g.tiles_y );
+	c->g.band_ty1 = std::min( ( rank + 1 ) * per, c->g.tiles_y );
+	c->rank = rank;
+	c->n_ranks = n_ranks;
+}
+
+extern "C" void gs2d_destroy( gs2d_ctx* c )
+{
+	if( !c )
+		return;
+	cudaSetDevice( c->device );
+	if( c->stream )
+		cudaStreamSynchronize( c->stream );
+	if( c->comm && g_nccl.CommDestroy )
+		g_nccl.CommDestroy( c->comm );
+	Buffers& b = c->b;
+	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.rect,  b.cnt,
+	                 b.scan_tmp,   b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.radix_hist, b.tile_range,
+	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
+	                 b.state,      c->dstage };
+	for( void* p : ptrs )
+		if( p )
+			cudaFree( p );
+	if( c->pinned )
+		cudaFreeHost( c->pinned );
+	if( c->h_state )
+		cudaFreeHost( c->h_state );
+	for( auto& e : c->ev )
+		if( e )
+			cudaEventDestroy( e );
+	if( c->stream )
+		cudaStreamDestroy( c->stream );
+	delete c;
+}
+
+extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_images, int device,
+                            const gs2d_params* params )
+{
+	if( !out )
+		return GS2D_ERR_INVALID;
+	*out = nullptr;
+	if( W <= 0 || H <= 0 || n_splats < 0 || n_images <= 0 || W > 65535 * GS2D_TILE || H > 65535 * GS2D_TILE )
+		return GS2D_ERR_INVALID;
+	if( (long long)n_splats * n_images > 0x7FFF0000ll || n_images > 65535 )
+		return GS2D_ERR_INVALID;
+	int n_dev = 0;
+	if( cudaGetDeviceCount( &n_dev ) != cudaSuccess || device < 0 || device >= n_dev )
+		return GS2D_ERR_NO_DEVICE;
+	cudaDeviceProp prop;
+	if( cudaGetDeviceProperties( &prop, device ) != cudaSuccess || prop.major != 10 )
+		return GS2D_ERR_NO_DEVICE; // the kernels are compiled for sm_100a only
+	gs2d_ctx* c = new gs2d_ctx();
+	c->device = device;
+	if( params )
+		c->hp = *params;
+	else
+		gs2d_default_params( &c->hp );
+	if( c->hp.bounds != 3.0f )
+	{
+		delete c;
+		return GS2D_ERR_INVALID; // the footprint solve hard-codes SPLAT_BOUNDS = 3 (main.cpp:7)
+	}
+	auto fail = [&]( int code ) {
+		gs2d_destroy( c );
+		return code;
+	};
+#define CKC( call )                                                                                                   \
+	do                                                                                                                \
+	{                                                                                                                 \
+		cudaError_t e_ = ( call );                                                                                    \
+		if( e_ != cudaSuccess )                                                                                       \
+		{                                                                                                             \
+			fprintf( stderr, "gs2d_create: %s -> %s\n", #call, cudaGetErrorString( e_ ) );                           \
+			return fail( e_ == cudaErrorMemoryAllocation ? GS2D_ERR_OOM : GS2D_ERR_CUDA );                            \
+		}                                                                                                             \
+	} while( 0 )
+	CKC( cudaSetDevice( device ) );
+	CKC( cudaStreamCreateWithFlags( &c->stream, cudaStreamNonBlocking ) );
+	for( auto& e : c->ev )
+		CKC( cudaEventCreate( &e ) );
+
+	Geometry& g = c->g;
+	g.W = W;
+	g.H = H;
+	g.n_splats = n_splats;
+	g.n_images = n_images;
+	g.n_total = n_splats * n_images;
+	g.n_pad = ( ( g.n_total + 3 ) / 4 ) * 4 + 4;
+	g.tiles_x = ( W + GS2D_TILE - 1 ) / GS2D_TILE;
+	g.tiles_y = ( H + GS2D_TILE - 1 ) / GS2D_TILE;
+	g.n_tiles_total = n_images * g.tiles_x * g.tiles_y;
+	g.min_throughput = c->hp.min_throughput;
+	set_band( c, 0, 1 );
+
+	Buffers& b = c->b;
+	const size_t plane_bytes = sizeof( float ) * (size_t)g.n_pad * GS2D_NPLANES;
+	const size_t n_px = (size_t)n_images * W * H;
+	const int nb = ( g.n_total + 255 ) / 256;
+	CKC( cudaMalloc( &b.params, plane_bytes ) );
+	CKC( cudaMalloc( &b.grads, plane_bytes ) );
+	CKC( cudaMalloc( &b.adam_m, plane_bytes ) );
+	CKC( cudaMalloc( &b.adam_v, plane_bytes ) );
+	CKC( cudaMalloc( &b.rec, sizeof( SplatRec ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.rect, sizeof( ushort4 ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.cnt, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.scan_tmp, sizeof( unsigned long long ) * ( 2 * (size_t)nb + 16 ) ) );
+	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );
+	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
+	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );
+	CKC( cudaMalloc( &b.loss_partial, sizeof( double ) * (size_t)g.n_tiles_total ) );
+	CKC( cudaMalloc( &b.live_slots, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
+	b.staged_slots = b.live_slots + GS2D_LIVE_SLOTS;
+	CKC( cudaMalloc( &b.stats, sizeof( unsigned long long ) * 2 ) );
+	CKC( cudaMalloc( &b.loss, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
+	b.mse_cap = 64;
+	CKC( cudaMalloc( &b.mse_ring, sizeof( double ) * (size_t)b.mse_cap * n_images ) );
+	CKC( cudaMalloc( &b.state, sizeof( DevState ) ) );
+	CKC( cudaMallocHost( &c->h_state, sizeof( DevState ) ) );
+	CKC( cudaMemset( b.params, 0, plane_bytes ) );
+	CKC( cudaMemset( b.grads, 0, plane_bytes ) );
+	CKC( cudaMemset( b.adam_m, 0, plane_bytes ) );
+	CKC( cudaMemset( b.adam_v, 0, plane_bytes ) );
+	CKC( cudaMemset( b.target, 0, sizeof( float4 ) * n_px ) );
+	CKC( cudaMemset( b.image, 0, sizeof( float4 ) * n_px ) );
+	CKC( cudaMemset( b.loss_partial, 0, sizeof( double ) * (size_t)g.n_tiles_total ) );
+	CKC( cudaMemset( b.live_slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
+	CKC( cudaMemset( b.stats, 0, sizeof( unsigned long long ) * 2 ) );
+	CKC( cudaMemset( b.loss, 0, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
+	DevState s0{};
+	s0.beta1t = 1.0f;
+	s0.beta2t = 1.0f;
+	CKC( cudaMemcpy( b.state, &s0, sizeof( s0 ), cudaMemcpyHostToDevice ) );
+	{
+		// ~17 tiles per splat at the reference's initial scales; start with twice that
+		int rc = alloc_keys( c, 40ull * (unsigned long long)std::max( g.n_total, 1 ) );
+		if( rc != GS2D_OK )
+			return fail( rc );
+	}
+#undef CKC
+	*out = c;
+	return GS2D_OK;
+}
+
+// ---- targets, state ---------------------------------------------------------------------------------------------
+extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgba )
+{
+	if( !c || !rgba || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	const size_t n_px = (size_t)c->g.W * c->g.H, bytes = n_px * sizeof( float4 );
+	int rc = ensure_staging( c, bytes );
+	if( rc )
+		return rc;
+	memcpy( c->pinned, rgba, bytes );
+	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, c->pinned, bytes, cudaMemcpyHostToDevice, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_set_target_rgba8( gs2d_ctx* c, int image, const uint8_t* rgba )
+{
+	if( !c || !rgba || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	const size_t n_px = (size_t)c->g.W * c->g.H, bytes = n_px * 4;
+	int rc = ensure_staging( c, bytes );
+	if( rc )
+		return rc;
+	memcpy( c->pinned, rgba, bytes );
+	CK( cudaMemcpyAsync( c->dstage, c->pinned, bytes, cudaMemcpyHostToDevice, c->stream ) );
+	c->launches += launch_u8_to_target( (const uint8_t*)c->dstage, c->b.target + (size_t)image * n_px, n_px, c->stream );
+	CK( cudaStreamSynchronize( c->stream ) );
+	return check_launch( c );
+}
+
+static int write_state( gs2d_ctx* c, float b1t, float b2t, int iteration )
+{
+	DevState s{};
+	s.beta1t = b1t;
+	s.beta2t = b2t;
+	s.iteration = iteration;
+	*c->h_state = s;
+	CK( cudaMemcpyAsync( c->b.state, c->h_state, sizeof( DevState ), cudaMemcpyHostToDevice, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	c->expected_iteration = iteration;
+	c->have_forward = false;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_init_reference( gs2d_ctx* c )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	c->launches += launch_init_reference( c->g, c->b, c->stream );
+	int rc = check_launch( c );
+	if( rc )
+		return rc;
+	return write_state( c, 1.0f, 1.0f, 0 );
+}
+
+extern "C" int gs2d_upload_state( gs2d_ctx* c, int image, const gs2d_splat* splats, const gs2d_splat_adam* adam,
+                                  float beta1t, float beta2t, int iteration )
+{
+	if( !c || ( !splats && c->g.n_splats > 0 ) || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	const size_t n = (size_t)c->g.n_splats;
+	const size_t sb = n * sizeof( gs2d_splat ), ab = n * sizeof( gs2d_splat_adam );
+	int rc = ensure_staging( c, sb + ab + 64 );
+	if( rc )
+		return rc;
+	if( n )
+	{
+		memcpy( c->pinned, splats, sb );
+		if( adam )
+			memcpy( (char*)c->pinned + sb, adam, ab );
+		CK( cudaMemcpyAsync( c->dstage, c->pinned, sb + ( adam ? ab : 0 ), cudaMemcpyHostToDevice, c->stream ) );
+		c->launches += launch_aos_to_soa( c->g, c->b, image, (const gs2d_splat*)c->dstage,
+		                                  adam ? (const gs2d_splat_adam*)( (char*)c->dstage + sb ) : nullptr, c->stream );
+		// gradients of a freshly uploaded state are zero (dSplats is value-initialised every iteration, main.cpp:550)
+		for( int f = 0; f < GS2D_NPLANES; f++ )
+			CK( cudaMemsetAsync( c->b.grads + (size_t)f * c->g.n_pad + (size_t)image * n, 0, sizeof( float ) * n,
+			                     c->stream ) );
+		rc = check_launch( c );
+		if( rc )
+			return rc;
+	}
+	return write_state( c, beta1t, beta2t, iteration );
+}
+
+static int fetch_state( gs2d_ctx* c )
+{
+	CK( cudaMemcpyAsync( c->h_state, c->b.state, sizeof( DevState ), cudaMemcpyDeviceToHost, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	return GS2D_OK;
+}
+
+static int download_aos( gs2d_ctx* c, int image, gs2d_splat* splats, gs2d_splat_adam* adam, gs2d_splat* grads )
+{
+	const size_t n = (size_t)c->g.n_splats;
+	if( n == 0 )
+		return GS2D_OK;
+	const size_t sb = n * sizeof( gs2d_splat ), ab = n * sizeof( gs2d_splat_adam );
+	int rc = ensure_staging( c, 2 * sb + ab + 64 );
+	if( rc )
+		return rc;
+	char* d = (char*)c->dstage;
+	c->launches += launch_soa_to_aos( c->g, c->b, image, splats ? (gs2d_splat*)d : nullptr,
+	                                  adam ? (gs2d_splat_adam*)( d + sb ) : nullptr,
+	                                  grads ? (gs2d_splat*)( d + sb + ab ) : nullptr, c->stream );
+	rc = check_launch( c );
+	if( rc )
+		return rc;
+	CK( cudaMemcpyAsync( c->pinned, c->dstage, 2 * sb + ab, cudaMemcpyDeviceToHost, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	char* h = (char*)c->pinned;
+	if( splats )
+		memcpy( splats, h, sb );
+	if( adam )
+		memcpy( adam, h + sb, ab );
+	if( grads )
+		memcpy( grads, h + sb + ab, sb );
+	return GS2D_OK;
+}
+
+static int resolve( gs2d_ctx* c ); // sync + capacity recovery, below
+
+extern "C" int gs2d_download_state( gs2d_ctx* c, int image, gs2d_splat* splats, gs2d_splat_adam* adam, float* beta1t,
+                                    float* beta2t, int* iteration )
+{
+	if( !c || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = resolve( c );
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	int rc2 = download_aos( c, image, splats, adam, nullptr );
+	if( rc2 )
+		return rc2;
+	if( beta1t )
+		*beta1t = c->h_state->beta1t;
+	if( beta2t )
+		*beta2t = c->h_state->beta2t;
+	if( iteration )
+		*iteration = c->h_state->iteration;
+	return rc;
+}
+
+extern "C" int gs2d_set_optimize_opacity( gs2d_ctx* c, int enabled )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	c->hp.optimize_opacity = enabled ? 1 : 0;
+	return GS2D_OK;
+}
+
+// ---- the iteration ----------------------------------------------------------------------------------------------
+static int enqueue_forward( gs2d_ctx* c )
+{
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr );
+	c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->stream );
+	c->launches += launch_finalize_loss( c->g, c->b, c->stream );
+	c->have_forward = true;
+	return check_launch( c );
+}
+
+static int enqueue_allreduce( gs2d_ctx* c )
+{
+	if( !c->comm )
+		return GS2D_OK;
+	// gradients of all 9 planes (padding included: zeros) and the per-image loss sums (+ the overflow vote)
+	int e1 = g_nccl.AllReduce( c->b.grads, c->b.grads, (size_t)c->g.n_pad * GS2D_NPLANES, NCCL_FLOAT32, NCCL_SUM, c->comm,
+	                           c->stream );
+	int e2 = g_nccl.AllReduce( c->b.loss, c->b.loss, (size_t)c->g.n_images + 1, NCCL_FLOAT64, NCCL_SUM, c->comm,
+	                           c->stream );
+	if( e1 || e2 )
+	{
+		snprintf( c->err, sizeof( c->err ), "ncclAllReduce failed: %s",
+		          g_nccl.GetErrorString ? g_nccl.GetErrorString( e1 ? e1 : e2 ) : "?" );
+		return GS2D_ERR_NCCL;
+	}
+	return GS2D_OK;
+}
+
+static int enqueue_iteration( gs2d_ctx* c )
+{
+	int rc = enqueue_forward( c );
+	if( rc )
+		return rc;
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, c->stream );
+	rc = enqueue_allreduce( c );
+	if( rc )
+		return rc;
+	c->launches += launch_advance( c->g, c->b, c->hp, c->stream );
+	c->launches += launch_adam( c->g, c->b, c->hp, c->stream );
+	c->expected_iteration++;
+	c->have_forward = false; // parameters changed: image/grads no longer correspond to them
+	return check_launch( c );
+}
+
+// Wait for everything enqueued; if an iteration was skipped because the key buffers were too small (on this or on
+// any other rank), grow them and run the missing iterations again.
+static int resolve( gs2d_ctx* c )
+{
+	for( int attempt = 0; attempt < 8; attempt++ )
+	{
+		int rc = fetch_state( c );
+		if( rc )
+			return rc;
+		const DevState& s = *c->h_state;
+		const long long missing = c->expected_iteration - (long long)s.iteration;
+		if( s.need_capacity == 0 && missing <= 0 )
+			return s.nonfinite ? GS2D_ERR_NONFINITE : GS2D_OK;
+		if( s.need_capacity )
+		{
+			rc = alloc_keys( c, s.need_capacity + s.need_capacity / 2 );
+			if( rc )
+				return rc;
+			CK( cudaMemsetAsync( &c->b.state->need_capacity, 0, sizeof( unsigned long long ), c->stream ) );
+		}
+		if( missing > 0 )
+		{
+			// the skipped iterations may have left partial gradients behind (ranks that did not overflow)
+			CK( cudaMemsetAsync( c->b.grads, 0, sizeof( float ) * (size_t)c->g.n_pad * GS2D_NPLANES, c->stream ) );
+			c->expected_iteration = s.iteration;
+			for( long long i = 0; i < missing; i++ )
+				if( ( rc = enqueue_iteration( c ) ) )
+					return rc;
+		}
+		else if( c->have_forward )
+		{
+			// a stand-alone gs2d_forward overflowed: redo it
+			if( ( rc = enqueue_forward( c ) ) )
+				return rc;
+		}
+	}
+	snprintf( c->err, sizeof( c->err ), "key capacity did not converge" );
+	return GS2D_ERR_OOM;
+}
+
+extern "C" int gs2d_step( gs2d_ctx* c, int n_iters, double* mse )
+{
+	if( !c || n_iters < 0 )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	Buffers& b = c->b;
+	if( mse && n_iters > b.mse_cap )
+	{
+		CK( cudaStreamSynchronize( c->stream ) );
+		cudaFree( b.mse_ring );
+		b.mse_ring = nullptr;
+		b.mse_cap = n_iters;
+		CK( cudaMalloc( &b.mse_ring, sizeof( double ) * (size_t)b.mse_cap * c->g.n_images ) );
+	}
+	CK( cudaMemsetAsync( &b.state->mse_slot, 0, sizeof( int ), c->stream ) );
+	CK( cudaEventRecord( c->ev[0], c->stream ) );
+	for( int i = 0; i < n_iters; i++ )
+	{
+		int rc = enqueue_iteration( c );
+		if( rc )
+			return rc;
+	}
+	CK( cudaEventRecord( c->ev[1], c->stream ) );
+	if( !mse )
+		return GS2D_OK;
+	int rc = resolve( c );
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	cudaEventElapsedTime( &c->last_ms, c->ev[0], c->ev[1] );
+	const size_t bytes = sizeof( double ) * (size_t)n_iters * c->g.n_images;
+	if( bytes )
+	{
+		int rc2 = ensure_staging( c, bytes );
+		if( rc2 )
+			return rc2;
+		CK( cudaMemcpyAsync( c->pinned, b.mse_ring, bytes, cudaMemcpyDeviceToHost, c->stream ) );
+		CK( cudaStreamSynchronize( c->stream ) );
+		memcpy( mse, c->pinned, bytes );
+	}
+	return rc;
+}
+
+extern "C" int gs2d_forward( gs2d_ctx* c )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = enqueue_forward( c );
+	if( rc )
+		return rc;
+	rc = resolve( c );
+	return rc == GS2D_ERR_NONFINITE ? GS2D_OK : rc;
+}
+
+extern "C" int gs2d_backward( gs2d_ctx* c )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	if( !c->have_forward )
+		return GS2D_ERR_STATE;
+	CK( cudaSetDevice( c->device ) );
+	CK( cudaMemsetAsync( c->b.grads, 0, sizeof( float ) * (size_t)c->g.n_pad * GS2D_NPLANES, c->stream ) );
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, true, c->stream );
+	int rc = check_launch( c );
+	if( rc )
+		return rc;
+	rc = enqueue_allreduce( c );
+	if( rc )
+		return rc;
+	CK( cudaStreamSynchronize( c->stream ) );
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_adam( gs2d_ctx* c )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	c->launches += launch_advance( c->g, c->b, c->hp, c->stream );
+	c->launches += launch_adam( c->g, c->b, c->hp, c->stream );
+	c->expected_iteration++;
+	c->have_forward = false;
+	int rc = check_launch( c );
+	if( rc )
+		return rc;
+	rc = fetch_state( c );
+	if( rc )
+		return rc;
+	return c->h_state->nonfinite ? GS2D_ERR_NONFINITE : GS2D_OK;
+}
+
+extern "C" int gs2d_download_image_rgba32f( gs2d_ctx* c, int image, float* rgba )
+{
+	if( !c || !rgba || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	const size_t n_px = (size_t)c->g.W * c->g.H, bytes = n_px * sizeof( float4 );
+	int rc = ensure_staging( c, bytes );
+	if( rc )
+		return rc;
+	CK( cudaMemcpyAsync( c->pinned, c->b.image + (size_t)image * n_px, bytes, cudaMemcpyDeviceToHost, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	memcpy( rgba, c->pinned, bytes );
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_download_grads( gs2d_ctx* c, int image, gs2d_splat* dsplats )
+{
+	if( !c || ( !dsplats && c->g.n_splats > 0 ) || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	return download_aos( c, image, nullptr, nullptr, dsplats );
+}
+
+extern "C" int gs2d_last_mse( gs2d_ctx* c, double* mse )
+{
+	if( !c || !mse )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = ensure_staging( c, sizeof( double ) * ( (size_t)c->g.n_images + 1 ) );
+	if( rc )
+		return rc;
+	CK( cudaMemcpyAsync( c->pinned, c->b.loss, sizeof( double ) * c->g.n_images, cudaMemcpyDeviceToHost, c->stream ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	const double* src = (const double*)c->pinned;
+	for( int i = 0; i < c->g.n_images; i++ )
+		mse[i] = src[i] / (double)( c->g.H * c->g.W * 3 ); // main.cpp:805
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_get_stats( gs2d_ctx* c, gs2d_stats* out )
+{
+	if( !c || !out )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = fetch_state( c );
+	if( rc )
+		return rc;
+	unsigned long long st[2] = { 0, 0 };
+	CK( cudaMemcpy( st, c->b.stats, sizeof( st ), cudaMemcpyDeviceToHost ) );
+	out->keys = c->h_state->n_keys;
+	out->live_pairs = st[0];
+	out->staged = st[1];
+	out->capacity = c->b.capacity;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_sync( gs2d_ctx* c )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = resolve( c );
+	if( rc == GS2D_OK || rc == GS2D_ERR_NONFINITE )
+		cudaEventElapsedTime( &c->last_ms, c->ev[0], c->ev[1] );
+	return rc;
+}
+
+extern "C" int gs2d_last_step_ms( gs2d_ctx* c, float* ms )
+{
+	if( !c || !ms )
+		return GS2D_ERR_INVALID;
+	*ms = c->last_ms;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_launch_count( gs2d_ctx* c, uint64_t* n )
+{
+	if( !c || !n )
+		return GS2D_ERR_INVALID;
+	*n = c->launches;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_profile_step( gs2d_ctx* c, float out_ms[6] )
+{
+	if( !c || !out_ms )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = resolve( c );
+	if( rc )
+		return rc;
+	cudaStream_t s = c->stream;
+	CK( cudaEventRecord( c->ev[2], s ) );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, c->ev[8] ); // ev[8]: after the key emit
+	CK( cudaEventRecord( c->ev[3], s ) );
+	c->launches += launch_forward( c->g, c->b, c->sorted_buf, s );
+	c->launches += launch_finalize_loss( c->g, c->b, s );
+	CK( cudaEventRecord( c->ev[4], s ) );
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, s );
+	CK( cudaEventRecord( c->ev[5], s ) );
+	rc = enqueue_allreduce( c );
+	if( rc )
+		return rc;
+	CK( cudaEventRecord( c->ev[6], s ) );
+	c->launches += launch_advance( c->g, c->b, c->hp, s );
+	c->launches += launch_adam( c->g, c->b, c->hp, s );
+	CK( cudaEventRecord( c->ev[7], s ) );
+	c->expected_iteration++;
+	c->have_forward = false;
+	rc = check_launch( c );
+	if( rc )
+		return rc;
+	rc = resolve( c );
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	cudaEventElapsedTime( &out_ms[0], c->ev[2], c->ev[8] );
+	cudaEventElapsedTime( &out_ms[1], c->ev[8], c->ev[3] );
+	cudaEventElapsedTime( &out_ms[2], c->ev[3], c->ev[4] );
+	cudaEventElapsedTime( &out_ms[3], c->ev[4], c->ev[5] );
+	cudaEventElapsedTime( &out_ms[4], c->ev[5], c->ev[6] );
+	cudaEventElapsedTime( &out_ms[5], c->ev[6], c->ev[7] );
+	return rc;
+}
+
+// ---- multi-GPU --------------------------------------------------------------------------------------------------
+extern "C" int gs2d_set_band( gs2d_ctx* c, int rank, int n_ranks )
+{
+	if( !c || n_ranks <= 0 || rank < 0 || rank >= n_ranks )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	CK( cudaStreamSynchronize( c->stream ) );
+	set_band( c, rank, n_ranks );
+	CK( cudaMemset( c->b.loss_partial, 0, sizeof( double ) * (size_t)c->g.n_tiles_total ) );
+	c->have_forward = false;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_comm_unique_id( uint8_t id[128] )
+{
+	if( !id || !nccl_load() )
+		return GS2D_ERR_NCCL;
+	ncclUniqueId_ u;
+	if( g_nccl.GetUniqueId( &u ) )
+		return GS2D_ERR_NCCL;
+	memcpy( id, u.internal, 128 );
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t id[128] )
+{
+	if( !c || !id || n_ranks <= 0 || rank < 0 || rank >= n_ranks )
+		return GS2D_ERR_INVALID;
+	if( !nccl_load() )
+	{
+		snprintf( c->err, sizeof( c->err ), "libnccl.so.2 not found" );
+		return GS2D_ERR_NCCL;
+	}
+	CK( cudaSetDevice( c->device ) );
+	int rc = gs2d_set_band( c, rank, n_ranks );
+	if( rc )
+		return rc;
+	if( n_ranks == 1 )
+		return GS2D_OK;
+	ncclUniqueId_ u;
+	memcpy( u.internal, id, 128 );
+	int e = g_nccl.CommInitRank( &c->comm, n_ranks, u, rank );
+	if( e )
+	{
+		snprintf( c->err, sizeof( c->err ), "ncclCommInitRank failed: %s",
+		          g_nccl.GetErrorString ? g_nccl.GetErrorString( e ) : "?" );
+		c->comm = nullptr;
+		return GS2D_ERR_NCCL;
+	}
+	return GS2D_OK;
+}

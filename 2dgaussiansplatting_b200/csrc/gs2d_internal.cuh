@@ -1,0 +1,191 @@
+// gs2d_internal.cuh — shared declarations of the sm_100a kernels behind include/gs2d.h.
+//
+// Device data layout (all in HBM, owned by gs2d_ctx):
+//   params / grads / adam_m / adam_v : 9 SoA planes of n_total_pad floats each, plane order == field order of the
+//       reference's Splat (main.cpp:85-93): pos.x pos.y sx sy rot color.r color.g color.b opacity.
+//       n_total = n_images * n_splats; global splat index g = image * n_splats + i.
+//   rec      : one 64-byte record per splat, rewritten every iteration by k_preprocess (SplatRec below)
+//   rect     : tile rectangle of the splat inside this rank's band (4 x u16), cnt: number of tiles in it
+//   keys/vals: (tile id, splat index) list entries, double-buffered for the LSD radix passes
+//   tile_range: [start,end) of every tile's list after the sort
+//   target / image : RGBA float32, row-major, n_images * H * W float4 (== pr::Image2DRGBA32, prp.cpp:751-756)
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gs2d.h"
+
+#define GS2D_TILE 16          // tile edge in pixels; one CTA of 256 threads per tile, one pixel per thread
+#define GS2D_BATCH 32         // list entries staged into shared memory per round
+#define GS2D_NPLANES 9
+#define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
+
+enum
+{
+	PL_PX = 0,
+	PL_PY,
+	PL_SX,
+	PL_SY,
+	PL_ROT,
+	PL_CR,
+	PL_CG,
+	PL_CB,
+	PL_OP
+};
+
+// 64-byte per-splat record (4 x float4). q0..q2 are what the forward pass reads; q3 holds the per-splat
+// invariants hoisted out of the backward pass (cos, sin, sx^-3, sy^-3, (sx^2-sy^2)/(sx^2 sy^2)).
+struct __align__( 16 ) SplatRec
+{
+	float px, py, a, b;        // q0: position, inv_cov[0][0], inv_cov[1][0] (== inv_cov[0][1])
+	float d, cr, cg, cb;       // q1: inv_cov[1][1], colour
+	float op;                  // q2: opacity
+	int begY, endY;            //     row range, main.cpp:490-491 (x86 truncation semantics)
+	float rotc;                //     (sx^2 - sy^2) / (sx^2 sy^2)
+	float cosT, sinT, isx3, isy3; // q3
+};
+static_assert( sizeof( SplatRec ) == 64, "SplatRec must be 64 bytes" );
+
+// Loop-carried scalars + flags, one per context, lives in device memory so that gs2d_step can be fully async.
+struct DevState
+{
+	float beta1t, beta2t;      // main.cpp:274-275
+	int iteration;             // main.cpp:278
+	int nonfinite;             // set by k_adam where the reference would abort() (main.cpp:752-785)
+	unsigned long long n_keys; // total list entries of the current iteration (written by the scan)
+	unsigned long long need_capacity; // != 0: the key buffers were too small; the iteration was skipped
+	int mse_slot;              // next slot of the mse ring written by k_finalize
+	int pad;
+};
+
+struct Geometry
+{
+	int W, H;
+	int n_splats;   // per image
+	int n_images;
+	int n_total;    // n_images * n_splats
+	int n_pad;      // plane stride (multiple of 4)
+	int tiles_x, tiles_y;    // per image
+	int band_ty0, band_ty1;  // this rank's tile rows [ty0, ty1)
+	int n_tiles_total;       // n_images * tiles_y * tiles_x  (key space)
+	float min_throughput;    // MIN_THROUGHPUT, main.cpp:8
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// Contraction-free float helpers. The reference build never fuses a*b+c (MSVC /fp:precise), and the
+// footprint / transmittance decisions are step functions of rounded values, so everything that feeds a decision is
+// written with these (nvcc never contracts the _rn intrinsics).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float xmul( float a, float b ) { return __fmul_rn( a, b ); }
+__device__ __forceinline__ float xadd( float a, float b ) { return __fadd_rn( a, b ); }
+__device__ __forceinline__ float xsub( float a, float b ) { return __fsub_rn( a, b ); }
+__device__ __forceinline__ float xdiv( float a, float b ) { return __fdiv_rn( a, b ); }
+__device__ __forceinline__ float xsqrt( float a ) { return __fsqrt_rn( a ); }
+
+// (int)f as the reference's x86 build does it (cvttss2si): toward zero; NaN / out of range -> INT_MIN.
+__device__ __forceinline__ int trunc_x86( float f )
+{
+	return ( f > -2147483648.0f && f < 2147483648.0f ) ? __float2int_rz( f ) : (int)0x80000000;
+}
+
+// exp_approx( -0.5f * d2 ), main.cpp:49-83.  1 + (-0.5*d2)/8 == fma(d2, -1/16, 1) bit for bit (the two scalings are
+// exact powers of two, so both forms round once).
+__device__ __forceinline__ float gauss_of_d2( float d2 )
+{
+	float t = __fmaf_rn( d2, -0.0625f, 1.0f );
+	float t2 = xmul( t, t );
+	float t4 = xmul( t2, t2 );
+	float t8 = xmul( t4, t4 );
+	return ( t < 0.00001814586175896693021059036255f ) ? 0.0f : t8;
+}
+
+// 16-bit coverage mask of tile row y for one splat: bit x set <=> pixel (tile_x0 + x, y) is inside the reference's
+// scan-line footprint (main.cpp:492-514): y in [begY, endY], x in [(int)(pos.x+u0), (int)(pos.x+u1)] where u0,u1
+// are the roots returned by solve_quadratic (main.cpp:171-185), x and y inside the image.
+__device__ __forceinline__ unsigned row_mask( float px, float py, float a, float b, float d, int begY, int endY,
+                                              int y, int tile_x0, int W, int H )
+{
+	if( y < begY || y > endY || y >= H )
+		return 0u;
+	float vy = xsub( xadd( (float)y, 0.5f ), py );
+	float qb = xmul( xmul( 2.0f, b ), vy );                    // 2.0f * b * vy
+	float qc = xsub( xmul( xmul( d, vy ), vy ), 9.0f );        // d * vy * vy - SPLAT_BOUNDS * SPLAT_BOUNDS
+	float det = xsub( xmul( qb, qb ), xmul( xmul( 4.0f, a ), qc ) ); // b*b - 4.0f*a*c
+	if( det < 0.0f )
+		return 0u;
+	float sgn = qb < 0.0f ? -1.0f : 1.0f;
+	float k = xmul( xsub( -qb, xmul( sgn, xsqrt( det ) ) ), 0.5f ); // ( -b - sign_of(b)*sqrtf(det) ) / 2.0f
+	float x0 = xdiv( k, a );
+	float x1 = xdiv( qc, k );
+	float u0 = ( x1 < x0 ) ? x1 : x0; // ss_min( x0, x1 )
+	float u1 = ( x0 < x1 ) ? x1 : x0; // ss_max( x0, x1 )
+	int begX = trunc_x86( xadd( px, u0 ) );
+	int endX = trunc_x86( xadd( px, u1 ) );
+	int lo = max( begX, tile_x0 ) - tile_x0;
+	int hi = min( min( endX, tile_x0 + GS2D_TILE - 1 ), W - 1 ) - tile_x0;
+	if( lo > hi )
+		return 0u;
+	return ( ( 2u << hi ) - 1u ) & ~( ( 1u << lo ) - 1u );
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// cp.async (LDGSTS) 16-byte gather into shared memory.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16( void* smem_dst, const void* gmem_src )
+{
+	unsigned s = (unsigned)__cvta_generic_to_shared( smem_dst );
+	asm volatile( "cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"( s ), "l"( gmem_src ) );
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile( "cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+	asm volatile( "cp.async.wait_group %0;\n" ::"n"( N ) );
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Launch wrappers (each returns the number of kernels it launched; errors are picked up by cudaGetLastError).
+// ---------------------------------------------------------------------------------------------------------------
+struct Buffers
+{
+	float* params;  // [9][n_pad]
+	float* grads;   // [9][n_pad]
+	float* adam_m;  // [9][n_pad]
+	float* adam_v;  // [9][n_pad]
+	SplatRec* rec;  // [n_total]
+	ushort4* rect;  // [n_total]
+	unsigned* cnt;  // [n_total]
+	unsigned long long* offs; // [n_total] exclusive scan of cnt
+	unsigned long long* scan_tmp;
+	unsigned* keys[2];
+	unsigned* vals[2];
+	unsigned long long capacity;
+	unsigned* radix_hist;     // [256][max_chunks]
+	unsigned max_chunks;
+	uint2* tile_range;        // [n_tiles_total]
+	float4* target;           // [n_images][H][W]
+	float4* image;            // [n_images][H][W]
+	double* loss_partial;     // [n_tiles_total]
+	unsigned long long* live_slots;   // [GS2D_LIVE_SLOTS]
+	unsigned long long* staged_slots; // [GS2D_LIVE_SLOTS], contiguous after live_slots
+	unsigned long long* stats;        // [2] live pairs, staged entries of the last forward (summed slots)
+	double* loss;             // [n_images]  sum over this rank's band of the squared 8-bit error
+	double* mse_ring;         // [mse_cap][n_images]
+	int mse_cap;
+	DevState* state;
+};
+
+int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
+int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
+int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
+                               cudaEvent_t after_emit );
+int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, cudaStream_t s );
+int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, cudaStream_t s );
+int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
+int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
+int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
+int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,
+                       const gs2d_splat_adam* adam_dev, cudaStream_t s );
+int launch_soa_to_aos( const Geometry& g, const Buffers& b, int image, gs2d_splat* splats_dev,
+                       gs2d_splat_adam* adam_dev, gs2d_splat* grads_dev, cudaStream_t s );
