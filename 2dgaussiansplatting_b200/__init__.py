@@ -45,6 +45,7 @@ ABI_SYMBOLS = [
     "gs2d_download_state", "gs2d_set_optimize_opacity", "gs2d_step", "gs2d_forward", "gs2d_backward", "gs2d_adam",
     "gs2d_download_image_rgba32f", "gs2d_download_grads", "gs2d_last_mse", "gs2d_get_stats", "gs2d_comm_unique_id",
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
+    "gs2d_set_profiling", "gs2d_get_profile",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
 ]
 
@@ -58,7 +59,9 @@ class Params(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = [("keys", C.c_uint64), ("live_pairs", C.c_uint64), ("staged", C.c_uint64), ("capacity", C.c_uint64)]
+    _fields_ = [("keys", C.c_uint64), ("live_pairs", C.c_uint64), ("staged", C.c_uint64), ("capacity", C.c_uint64),
+                ("live_pairs_sum", C.c_uint64), ("staged_sum", C.c_uint64), ("keys_sum", C.c_uint64),
+                ("n_forwards", C.c_uint64)]
 
 
 class Gs2dError(RuntimeError):
@@ -108,6 +111,8 @@ def load_library():
     L.gs2d_set_band.argtypes = [vp, i, i]
     L.gs2d_last_step_ms.argtypes = [vp, C.POINTER(f)]
     L.gs2d_profile_step.argtypes = [vp, C.POINTER(f * 6)]
+    L.gs2d_set_profiling.argtypes = [vp, i]
+    L.gs2d_get_profile.argtypes = [vp, C.POINTER(C.c_double * 6), C.POINTER(C.c_longlong)]
     L.gs2d_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.gs2d_sync.argtypes = [vp]
     L.gs2d_microbench_fp32.argtypes = [i, C.POINTER(C.c_double)]
@@ -286,7 +291,7 @@ class Fitter:
     def stats(self):
         s = Stats()
         self._ck(self.lib.gs2d_get_stats(self._ctx, C.byref(s)))
-        return {"keys": s.keys, "live_pairs": s.live_pairs, "staged": s.staged, "capacity": s.capacity}
+        return {f: getattr(s, f) for f, _ in Stats._fields_}
 
     def last_step_ms(self):
         ms = C.c_float()
@@ -298,6 +303,23 @@ class Fitter:
         self._ck(self.lib.gs2d_profile_step(self._ctx, C.byref(out)), allow_nonfinite=True)
         names = ["preprocess_emit", "sort", "forward", "backward", "allreduce", "adam"]
         return dict(zip(names, [float(v) for v in out]))
+
+    GROUPS = ["preprocess_emit", "sort", "forward", "backward", "allreduce", "adam"]
+
+    def set_profiling(self, enable=True):
+        """Bracket every iteration of step() with CUDA events on the library's stream (resets the sums)."""
+        self._ck(self.lib.gs2d_set_profiling(self._ctx, int(bool(enable))))
+
+    def get_profile(self):
+        """-> ({group: mean ms per iteration}, iterations measured) since set_profiling()."""
+        sums, n = (C.c_double * 6)(), C.c_longlong()
+        self._ck(self.lib.gs2d_get_profile(self._ctx, C.byref(sums), C.byref(n)), allow_nonfinite=True)
+        k = max(n.value, 1)
+        return {g: sums[j] / k for j, g in enumerate(self.GROUPS)}, n.value
+
+    def set_target_u8_ptr(self, ptr, image=0):
+        """Target from a raw host pointer (e.g. a pinned torch tensor's data_ptr()): H*W*4 bytes RGBA8."""
+        self._ck(self.lib.gs2d_set_target_rgba8(self._ctx, image, C.c_void_p(ptr)))
 
     def launch_count(self):
         n = C.c_uint64()

@@ -37,12 +37,19 @@ __global__ void __launch_bounds__( 256 ) k_finalize_loss( Geometry g, const doub
 	// overflow vote: summed over ranks together with the loss, so that every rank skips the same iterations
 	if( img == 0 && threadIdx.x == 0 )
 		loss[g.n_images] = st->need_capacity ? 1.0 : 0.0;
+	// stats: [0] live pairs, [1] staged entries of this forward; [2],[3] their running sums; [4] sum of keys; [5] forwards
 	if( img == 0 && threadIdx.x < 2 )
 	{
 		unsigned long long a = 0;
 		for( int i = 0; i < GS2D_LIVE_SLOTS; i++ )
 			a += slots[threadIdx.x * GS2D_LIVE_SLOTS + i];
 		stats[threadIdx.x] = a;
+		stats[2 + threadIdx.x] += a;
+	}
+	if( img == 0 && threadIdx.x == 2 && !st->need_capacity )
+	{
+		stats[4] += st->n_keys;
+		stats[5] += 1ull;
 	}
 }
 

@@ -86,6 +86,17 @@ struct gs2d_ctx
 
 	ncclComm_t comm = nullptr;
 	int rank = 0, n_ranks = 1;
+
+	// per-iteration CUDA-event profiling (gs2d_set_profiling): 7 events per enqueued iteration
+	struct ProfRec
+	{
+		cudaEvent_t ev[7];
+	};
+	std::vector<ProfRec> prof_pool;
+	size_t prof_used = 0;
+	bool profiling = false;
+	double prof_sum[6] = { 0, 0, 0, 0, 0, 0 };
+	long long prof_iters = 0;
 };
 
 #define CK( call )                                                                                                    \
@@ -225,6 +236,9 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	for( auto& e : c->ev )
 		if( e )
 			cudaEventDestroy( e );
+	for( auto& r : c->prof_pool )
+		for( auto& e : r.ev )
+			cudaEventDestroy( e );
 	if( c->stream )
 		cudaStreamDestroy( c->stream );
 	delete c;
@@ -307,7 +321,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.loss_partial, sizeof( double ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.live_slots, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
 	b.staged_slots = b.live_slots + GS2D_LIVE_SLOTS;
-	CKC( cudaMalloc( &b.stats, sizeof( unsigned long long ) * 2 ) );
+	CKC( cudaMalloc( &b.stats, sizeof( unsigned long long ) * 8 ) );
 	CKC( cudaMalloc( &b.loss, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
 	b.mse_cap = 64;
 	CKC( cudaMalloc( &b.mse_ring, sizeof( double ) * (size_t)b.mse_cap * n_images ) );
@@ -321,7 +335,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMemset( b.image, 0, sizeof( float4 ) * n_px ) );
 	CKC( cudaMemset( b.loss_partial, 0, sizeof( double ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMemset( b.live_slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
-	CKC( cudaMemset( b.stats, 0, sizeof( unsigned long long ) * 2 ) );
+	CKC( cudaMemset( b.stats, 0, sizeof( unsigned long long ) * 8 ) );
 	CKC( cudaMemset( b.loss, 0, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
 	DevState s0{};
 	s0.beta1t = 1.0f;
@@ -339,6 +353,17 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 }
 
 // ---- targets, state ---------------------------------------------------------------------------------------------
+// Host pointer already page-locked (cudaMallocHost / cudaHostRegister / torch pin_memory)? Then DMA straight from it.
+static const void* h2d_source( gs2d_ctx* c, const void* user, size_t bytes )
+{
+	cudaPointerAttributes attr;
+	if( cudaPointerGetAttributes( &attr, user ) == cudaSuccess && attr.type == cudaMemoryTypeHost )
+		return user;
+	cudaGetLastError();
+	memcpy( c->pinned, user, bytes );
+	return c->pinned;
+}
+
 extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgba )
 {
 	if( !c || !rgba || image < 0 || image >= c->g.n_images )
@@ -348,8 +373,8 @@ extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgb
 	int rc = ensure_staging( c, bytes );
 	if( rc )
 		return rc;
-	memcpy( c->pinned, rgba, bytes );
-	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, c->pinned, bytes, cudaMemcpyHostToDevice, c->stream ) );
+	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice,
+	                     c->stream ) );
 	CK( cudaStreamSynchronize( c->stream ) );
 	return GS2D_OK;
 }
@@ -363,8 +388,7 @@ extern "C" int gs2d_set_target_rgba8( gs2d_ctx* c, int image, const uint8_t* rgb
 	int rc = ensure_staging( c, bytes );
 	if( rc )
 		return rc;
-	memcpy( c->pinned, rgba, bytes );
-	CK( cudaMemcpyAsync( c->dstage, c->pinned, bytes, cudaMemcpyHostToDevice, c->stream ) );
+	CK( cudaMemcpyAsync( c->dstage, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice, c->stream ) );
 	c->launches += launch_u8_to_target( (const uint8_t*)c->dstage, c->b.target + (size_t)image * n_px, n_px, c->stream );
 	CK( cudaStreamSynchronize( c->stream ) );
 	return check_launch( c );
@@ -522,18 +546,59 @@ static int enqueue_allreduce( gs2d_ctx* c )
 
 static int enqueue_iteration( gs2d_ctx* c )
 {
-	int rc = enqueue_forward( c );
+	cudaStream_t s = c->stream;
+	gs2d_ctx::ProfRec* pr = nullptr;
+	if( c->profiling )
+	{
+		if( c->prof_used == c->prof_pool.size() )
+		{
+			gs2d_ctx::ProfRec r;
+			for( auto& e : r.ev )
+				CK( cudaEventCreate( &e ) );
+			c->prof_pool.push_back( r );
+		}
+		pr = &c->prof_pool[c->prof_used++];
+	}
+#define PROF( i )                                                                                                     \
+	if( pr )                                                                                                          \
+	cudaEventRecord( pr->ev[i], s )
+	PROF( 0 );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr );
+	PROF( 2 );
+	c->launches += launch_forward( c->g, c->b, c->sorted_buf, s );
+	c->launches += launch_finalize_loss( c->g, c->b, s );
+	PROF( 3 );
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, s );
+	PROF( 4 );
+	int rc = enqueue_allreduce( c );
 	if( rc )
 		return rc;
-	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, c->stream );
-	rc = enqueue_allreduce( c );
-	if( rc )
-		return rc;
-	c->launches += launch_advance( c->g, c->b, c->hp, c->stream );
-	c->launches += launch_adam( c->g, c->b, c->hp, c->stream );
+	PROF( 5 );
+	c->launches += launch_advance( c->g, c->b, c->hp, s );
+	c->launches += launch_adam( c->g, c->b, c->hp, s );
+	PROF( 6 );
+#undef PROF
 	c->expected_iteration++;
 	c->have_forward = false; // parameters changed: image/grads no longer correspond to them
 	return check_launch( c );
+}
+
+// everything enqueued has completed: fold the recorded events into the per-group sums
+static void collect_profile( gs2d_ctx* c )
+{
+	for( size_t i = 0; i < c->prof_used; i++ )
+	{
+		const gs2d_ctx::ProfRec& r = c->prof_pool[i];
+		for( int k = 0; k < 6; k++ )
+		{
+			float ms = 0.0f;
+			if( cudaEventElapsedTime( &ms, r.ev[k], r.ev[k + 1] ) == cudaSuccess )
+				c->prof_sum[k] += ms;
+		}
+		c->prof_iters++;
+	}
+	cudaGetLastError();
+	c->prof_used = 0;
 }
 
 // Wait for everything enqueued; if an iteration was skipped because the key buffers were too small (on this or on
@@ -548,7 +613,10 @@ static int resolve( gs2d_ctx* c )
 		const DevState& s = *c->h_state;
 		const long long missing = c->expected_iteration - (long long)s.iteration;
 		if( s.need_capacity == 0 && missing <= 0 )
+		{
+			collect_profile( c );
 			return s.nonfinite ? GS2D_ERR_NONFINITE : GS2D_OK;
+		}
 		if( s.need_capacity )
 		{
 			rc = alloc_keys( c, s.need_capacity + s.need_capacity / 2 );
@@ -714,12 +782,16 @@ extern "C" int gs2d_get_stats( gs2d_ctx* c, gs2d_stats* out )
 	int rc = fetch_state( c );
 	if( rc )
 		return rc;
-	unsigned long long st[2] = { 0, 0 };
+	unsigned long long st[8] = { 0 };
 	CK( cudaMemcpy( st, c->b.stats, sizeof( st ), cudaMemcpyDeviceToHost ) );
 	out->keys = c->h_state->n_keys;
 	out->live_pairs = st[0];
 	out->staged = st[1];
 	out->capacity = c->b.capacity;
+	out->live_pairs_sum = st[2];
+	out->staged_sum = st[3];
+	out->keys_sum = st[4];
+	out->n_forwards = st[5];
 	return GS2D_OK;
 }
 
@@ -750,44 +822,54 @@ extern "C" int gs2d_launch_count( gs2d_ctx* c, uint64_t* n )
 	return GS2D_OK;
 }
 
+extern "C" int gs2d_set_profiling( gs2d_ctx* c, int enable )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = resolve( c );
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	c->profiling = enable != 0;
+	if( enable )
+		CK( cudaMemset( c->b.stats + 2, 0, sizeof( unsigned long long ) * 6 ) );
+	for( double& v : c->prof_sum )
+		v = 0.0;
+	c->prof_iters = 0;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_get_profile( gs2d_ctx* c, double sums_ms[6], long long* n_iters )
+{
+	if( !c || !sums_ms || !n_iters )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	int rc = resolve( c );
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	for( int k = 0; k < 6; k++ )
+		sums_ms[k] = c->prof_sum[k];
+	*n_iters = c->prof_iters;
+	return GS2D_OK;
+}
+
 extern "C" int gs2d_profile_step( gs2d_ctx* c, float out_ms[6] )
 {
 	if( !c || !out_ms )
 		return GS2D_ERR_INVALID;
-	CK( cudaSetDevice( c->device ) );
-	int rc = resolve( c );
+	const bool was = c->profiling;
+	int rc = gs2d_set_profiling( c, 1 );
 	if( rc )
 		return rc;
-	cudaStream_t s = c->stream;
-	CK( cudaEventRecord( c->ev[2], s ) );
-	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, c->ev[8] ); // ev[8]: after the key emit
-	CK( cudaEventRecord( c->ev[3], s ) );
-	c->launches += launch_forward( c->g, c->b, c->sorted_buf, s );
-	c->launches += launch_finalize_loss( c->g, c->b, s );
-	CK( cudaEventRecord( c->ev[4], s ) );
-	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, s );
-	CK( cudaEventRecord( c->ev[5], s ) );
-	rc = enqueue_allreduce( c );
+	rc = enqueue_iteration( c );
 	if( rc )
 		return rc;
-	CK( cudaEventRecord( c->ev[6], s ) );
-	c->launches += launch_advance( c->g, c->b, c->hp, s );
-	c->launches += launch_adam( c->g, c->b, c->hp, s );
-	CK( cudaEventRecord( c->ev[7], s ) );
-	c->expected_iteration++;
-	c->have_forward = false;
-	rc = check_launch( c );
-	if( rc )
-		return rc;
-	rc = resolve( c );
-	if( rc && rc != GS2D_ERR_NONFINITE )
-		return rc;
-	cudaEventElapsedTime( &out_ms[0], c->ev[2], c->ev[8] );
-	cudaEventElapsedTime( &out_ms[1], c->ev[8], c->ev[3] );
-	cudaEventElapsedTime( &out_ms[2], c->ev[3], c->ev[4] );
-	cudaEventElapsedTime( &out_ms[3], c->ev[4], c->ev[5] );
-	cudaEventElapsedTime( &out_ms[4], c->ev[5], c->ev[6] );
-	cudaEventElapsedTime( &out_ms[5], c->ev[6], c->ev[7] );
+	double sums[6];
+	long long n = 0;
+	rc = gs2d_get_profile( c, sums, &n );
+	for( int k = 0; k < 6; k++ )
+		out_ms[k] = n ? (float)( sums[k] / (double)n ) : 0.0f;
+	c->profiling = was;
 	return rc;
 }
 

@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""bench.py — fit iterations/s (forward + backward + Adam) of the B200-native 2D Gaussian-splatting engine.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size 4096] [--splats 1000000]
+
+Workload (BASELINE.json metric / configs[2]): synthetic 4096x4096 RGB target, 1 M Gaussians initialised with the
+reference's own init() formula (main.cpp:280-305), lr 0.05, opacity not optimised. One "step" = one whole loop body of
+the reference (main.cpp:414-809): bin + sort, forward blend, loss, backward, [gradient all-reduce], Adam + clamps.
+N > 1 (launched by torchrun, one process per GPU): the image is split into tile-row bands, one per rank, and the
+per-Gaussian gradients are all-reduced over NCCL before Adam -> the total work is fixed ("strong" scaling).
+
+Prints ONE JSON line (rank 0). `value` = device-timed iterations/s with all inputs resident in HBM; `e2e` = the same
+metric through the C ABI with HOST buffers: every step uploads the RGBA8 target from pinned host memory
+(gs2d_set_target_rgba8, the reference's own ingest format, prp.cpp:179-193 + :796-807) and reads the mse back.
+
+--impl reference: the reference's own CPU implementation of the path, single thread (the reference is
+single-threaded), on the box's host cores. oracle/_ref/ref_main (the unmodified main.cpp) is hard-wired to one JPEG
+and 1024 splats, so at this size the function-ised restatement oracle/gs2d_oracle.c is timed (bit-identical to
+main.cpp, tests/test_oracle.py); each step is a bounded sample (1/16 of the workload at equal density).
+"""
+import argparse
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_FWD, FLOP_BWD = 27.0, 86.0  # per live (pixel, splat) pair, hoisted counts of SURVEY.md §8(d)
+ADAM_BYTES = 288.0               # per Gaussian: 8 planes x (p,g,m,v read + p,m,v,g write) + opacity plane p,g rw
+SAMPLE_DIV = 16                  # CPU sample = 1/16 of the workload (same Gaussian density)
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+
+    NAMES = {
+        0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x10: "sync_boost",
+        0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+        0x100: "display_clock_setting",
+    }
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.NAMES.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_sample(size, splats, iters):
+    """Time the CPU oracle (the reference's algorithm, 1 thread) on 1/SAMPLE_DIV of the workload at equal density.
+    Returns (equivalent full-workload it/s, description, seconds per sample iteration)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
+
+    gs2d = importlib.import_module("2dgaussiansplatting_b200")
+    side = int(round(size / SAMPLE_DIV ** 0.5))
+    n = max(1, splats // SAMPLE_DIV)
+    target = gs2d.synth_target(side, side, seed=1)
+    st = ob.State(side, side, n)
+    st.step(target)  # page in
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        st.step(target)
+    dt = (time.perf_counter() - t0) / iters
+    desc = (f"{iters} iterations of a {side}x{side} window with {n} Gaussians (1/{SAMPLE_DIV} of the workload at equal "
+            f"density, {dt:.2f} s each); value = sample it/s / {SAMPLE_DIV}")
+    return 1.0 / (dt * SAMPLE_DIV), desc, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    t_first = time.perf_counter()
+    # warm-up steps and timed steps are both sample iterations
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
+
+    gs2d = importlib.import_module("2dgaussiansplatting_b200")
+    side = int(round(args.size / SAMPLE_DIV ** 0.5))
+    n = max(1, args.splats // SAMPLE_DIV)
+    target = gs2d.synth_target(side, side, seed=1)
+    st = ob.State(side, side, n)
+    for _ in range(args.warmup):
+        st.step(target)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st.step(target)
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    value = 1.0 / (dt * SAMPLE_DIV)
+    sample = (f"each step = one iteration of a {side}x{side} window with {n} Gaussians (1/{SAMPLE_DIV} of the "
+              f"workload at equal density, {dt:.2f} s); value = sample it/s / {SAMPLE_DIV}")
+    line = {
+        "impl": "reference", "metric": "fit_iters_per_sec", "value": value, "unit": "it/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * SAMPLE_DIV * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": "it/s", "cores": 1, "kind": "port", "sample": sample,
+                         "host_cores_available": os.cpu_count()},
+        "e2e": {"value": value, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "wall_s": time.perf_counter() - t_first,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, n_gpus):
+    return {
+        "workload": f"synthetic {args.size}x{args.size} RGB target, {args.splats} Gaussians (BASELINE configs[2])",
+        "image": [args.size, args.size], "n_gaussians": args.splats, "init": "reference init() main.cpp:280-305",
+        "optimize_opacity": False, "lr": 0.05,
+        "parallelism": "single GPU" if n_gpus == 1 else f"{n_gpus} tile-row bands + NCCL all-reduce of 9 gradient planes",
+        "l2_policy": "no flush: per-iteration inputs (target 268 MB, image 268 MB, key lists >250 MB) exceed the 126 MB L2",
+    }
+
+
+def run_ours(args):
+    import torch
+
+    gs2d = importlib.import_module("2dgaussiansplatting_b200")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one process per GPU)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    S, N, K, W = args.size, args.splats, args.steps, args.warmup
+    target = gs2d.synth_target(S, S, seed=1)
+    pinned_u8 = torch.empty((S, S, 4), dtype=torch.uint8, pin_memory=True)
+    pinned_u8.numpy()[...] = np.rint(target * 255.0).astype(np.uint8)  # 8-bit target, as a decoded JPEG would be
+
+    fit = gs2d.Fitter(S, S, N, device=local_rank)
+    if world > 1:
+        box = [gs2d.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        fit.comm_init(rank, world, box[0])
+    fit.set_target_u8_ptr(pinned_u8.data_ptr())
+    fit.restart()
+
+    peaks = measured_peaks()
+    fp32_peak = hbm_peak_local = None
+    if rank == 0:
+        fp32_peak, hbm_peak_local = gs2d.microbench(local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident run: `value` ---------------------------------------------------------------------------
+    fit.step(max(W, 3))  # warm-up (>= 3), also grows the key buffers to their steady size
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    fit.set_profiling(True)
+    launches0 = fit.launch_count()
+    t0 = time.perf_counter()
+    fit.step(K, want_mse=False)
+    fit.sync()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    dev_ms = fit.last_step_ms()  # CUDA events on the library's stream around the K iterations
+    prof, n_prof = fit.get_profile()
+    stats = fit.stats()  # running sums since set_profiling(True)
+    fit.set_profiling(False)
+    clocks = sampler.stop()
+    launches = fit.launch_count() - launches0
+    barrier()
+    t = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device="cuda")
+    live = torch.tensor([float(stats["live_pairs_sum"]), float(stats["keys_sum"]), float(stats["n_forwards"])],
+                        dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(live, op=dist.ReduceOp.SUM)
+        live[2] /= world
+    dev_ms, wall_ms = float(t[0]), float(t[1])
+    ms_per_step = dev_ms / K
+    value = 1e3 / ms_per_step
+    n_fw = max(float(live[2]), 1.0)
+    live_per_it, keys_per_it = float(live[0]) / n_fw, float(live[1]) / n_fw
+
+    # ---- end to end through the C ABI with host buffers: `e2e` --------------------------------------------------
+    Ke = max(3, min(K, args.e2e_steps))
+    barrier()
+    t0 = time.perf_counter()
+    mse_last = None
+    for _ in range(Ke):
+        fit.set_target_u8_ptr(pinned_u8.data_ptr())  # H2D of the step's input from pinned host memory
+        mse_last = fit.step(1)                        # D2H of the step's result (mse)
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / Ke
+    te = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_ms = float(te[0])
+
+    if rank != 0:
+        fit.close()
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel ------------------------------------------------------------------------
+    hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+    kern = {}
+    if prof["forward"] > 0:
+        a = FLOP_FWD * live_per_it / world / (prof["forward"] * 1e-3) / 1e12
+        kern["k_forward"] = {"ms": prof["forward"], "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
+                             "unit": "TFLOP/s", "frac": a / fp32_peak}
+    if prof["backward"] > 0:
+        a = FLOP_BWD * live_per_it / world / (prof["backward"] * 1e-3) / 1e12
+        kern["k_backward"] = {"ms": prof["backward"], "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
+                              "unit": "TFLOP/s", "frac": a / fp32_peak}
+    if prof["sort"] > 0:
+        tiles = ((S + 15) // 16) ** 2
+        passes = max(1, -(-max(1, (tiles - 1).bit_length()) // 8))
+        b = keys_per_it / world * (passes * 24.0 + 4.0)  # per pass: hist read 4 + scatter read 8 + write 8 (+4 vals)...
+        a = b / (prof["sort"] * 1e-3) / 1e9
+        kern["radix_sort"] = {"ms": prof["sort"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": a / hbm_peak, "passes": passes}
+    if prof["adam"] > 0:
+        a = ADAM_BYTES * N / (prof["adam"] * 1e-3) / 1e9
+        kern["k_adam"] = {"ms": prof["adam"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
+                          "frac": a / hbm_peak}
+    kern["preprocess_emit"] = {"ms": prof["preprocess_emit"]}
+    kern["allreduce"] = {"ms": prof["allreduce"]}
+    dom = max((k for k in kern if "frac" in kern[k]), key=lambda k: kern[k]["ms"])
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(dom)
+    except Exception:
+        pass
+    roofline = {"kernel": dom, "bound": kern[dom]["bound"], "achieved": kern[dom]["achieved"], "peak": kern[dom]["peak"],
+                "unit": kern[dom]["unit"], "frac": kern[dom]["frac"], "traffic": traffic,
+                "peak_source": ("gs2d_microbench_fp32 on this device (FP32 FMA issue rate; MEASURED_PEAKS.json has no "
+                                "FP32 figure)") if kern[dom]["bound"] == "fp32_issue" else hbm_src,
+                "algorithmic_work": "27 (fwd) / 86 (bwd) flop per live (pixel,splat) pair x live pairs counted on the device",
+                "live_pairs_per_iteration": live_per_it, "keys_per_iteration": keys_per_it,
+                "hbm_copy_gbs_this_device": hbm_peak_local, "kernels": kern}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, desc, _ = cpu_sample(S, N, args.cpu_iters)
+        cpu = {"value": v, "unit": "it/s", "cores": 1, "kind": "port", "sample": desc,
+               "host_cores_available": os.cpu_count()}
+
+    line = {
+        "metric": "fit_iters_per_sec", "value": value, "unit": "it/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+        "clocks": clocks, "wall_ms_per_step": wall_ms / K,
+        "e2e": {"value": 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": S * S * 4, "d2h_bytes_per_step": 8,
+                "ms_per_step": e2e_ms, "steps": Ke,
+                "what": "per step: gs2d_set_target_rgba8 from pinned host memory + gs2d_step(1, &mse)"},
+        "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "last_mse": float(mse_last[0, 0]) if mse_last is not None else None,
+    }
+    print(json.dumps(line), flush=True)
+    fit.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=4096)
+    ap.add_argument("--splats", type=int, default=1_000_000)
+    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--cpu-iters", type=int, default=10)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps > 40:
+            args.steps = 40  # bounded: ~1 s per sample step on one core
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -84,6 +84,10 @@ typedef struct gs2d_stats
 	uint64_t live_pairs;    /* (pixel, splat) pairs blended with T >= min_throughput, forward pass */
 	uint64_t staged;        /* list entries actually staged by the forward kernel before tile termination */
 	uint64_t capacity;      /* current capacity of the key buffers (entries) */
+	uint64_t live_pairs_sum; /* running sums over all forwards since create / the last gs2d_set_profiling */
+	uint64_t staged_sum;
+	uint64_t keys_sum;
+	uint64_t n_forwards;
 } gs2d_stats;
 
 typedef struct gs2d_ctx gs2d_ctx;
@@ -146,6 +150,11 @@ int gs2d_last_step_ms( gs2d_ctx* ctx, float* ms );
 /* Per-kernel-group device times of one extra profiled iteration (does advance the fit by one iteration):
  * out[0]=preprocess+scan+emit, [1]=sort, [2]=forward, [3]=backward, [4]=allreduce, [5]=adam+finalise. */
 int gs2d_profile_step( gs2d_ctx* ctx, float out_ms[6] );
+/* Continuous profiling: while enabled, every iteration enqueued by gs2d_step is bracketed by CUDA events on the
+ * context's stream; gs2d_get_profile waits for the stream and returns the summed device time of each kernel group
+ * (same order as gs2d_profile_step) and the number of iterations measured. gs2d_set_profiling resets the sums. */
+int gs2d_set_profiling( gs2d_ctx* ctx, int enable );
+int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
 /* Number of kernel launches the library has issued on this context so far. */
 int gs2d_launch_count( gs2d_ctx* ctx, uint64_t* n );
 
