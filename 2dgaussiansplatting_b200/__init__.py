@@ -18,7 +18,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgs2d.so")
+LIB_PATH = os.environ.get("GS2D_LIB") or os.path.join(_HERE, "libgs2d.so")  # GS2D_LIB: developer override
 
 # the reference's AoS types (main.cpp:85-93, :158-166)
 SPLAT_DTYPE = np.dtype(

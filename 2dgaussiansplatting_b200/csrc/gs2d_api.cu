@@ -61,6 +61,20 @@ enum
 	NCCL_SUM = 0
 };
 
+int gs2d_pixels_per_thread( int which )
+{
+	static int cached[2] = { 0, 0 };
+	if( !cached[which] )
+	{
+		const char* e = getenv( which ? "GS2D_PPT_BWD" : "GS2D_PPT_FWD" );
+		int v = e ? atoi( e ) : 0;
+		if( v != 1 && v != 2 && v != 4 && v != 8 )
+			v = which ? GS2D_PPT_BWD_DEFAULT : GS2D_PPT_FWD_DEFAULT;
+		cached[which] = v;
+	}
+	return cached[which];
+}
+
 // ---- context ----------------------------------------------------------------------------------------------------
 struct gs2d_ctx
 {

@@ -19,6 +19,8 @@
 #define GS2D_TILE 16          // tile edge in pixels; one CTA of 256 threads per tile, one pixel per thread
 #define GS2D_BATCH 32         // list entries staged into shared memory per round
 #define GS2D_NPLANES 9
+#define GS2D_PPT_FWD_DEFAULT 8   // pixels per thread, forward blend (8 = one warp per tile)
+#define GS2D_PPT_BWD_DEFAULT 8   // pixels per thread, backward blend
 #define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
 
 enum
@@ -176,6 +178,8 @@ struct Buffers
 	DevState* state;
 };
 
+// pixels per thread of the blend kernels: which = 0 forward, 1 backward (env GS2D_PPT_FWD / GS2D_PPT_BWD override)
+int gs2d_pixels_per_thread( int which );
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
