@@ -18,7 +18,7 @@
 #define BWD_CONST_SMEM 1   // keep the per-pixel constants (final colour, dL/dC) in shared memory instead of registers
 #endif
 #ifndef BWD_MINB
-#define BWD_MINB 1
+#define BWD_MINB 16   // P = 8: cap at 128 registers -> 16 resident warps per SM (measured best)
 #endif
 
 // Sum 8 values over the 32 lanes with 9 shuffles. On return, lane L holds the total of value index
@@ -59,7 +59,7 @@ struct BwdExtra
 };
 
 template <int P, bool OPACITY>
-__global__ void __launch_bounds__( BlendCfg<P>::NT, BWD_MINB ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
+__global__ void __launch_bounds__( BlendCfg<P>::NT, P == 8 ? BWD_MINB : 1 ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
                                                                  const unsigned* __restrict__ vals,
                                                                  const uint2* __restrict__ tile_range,
                                                                  const float4* __restrict__ target,
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__( BlendCfg<P>::NT, BWD_MINB ) k_backward( Geome
 						Pb[j] = xadd( Pb[j], xmul( tcb, alpha ) );
 						// S = colour from behind, main.cpp:627;  dC/dalpha = c*T - S/(1 - alpha + 1e-15), main.cpp:628
 						const float oma = xsub( 1.0f, alpha );
-						const float inv = __frcp_rn( xadd( oma, 1.0e-15f ) );
+						const float inv = __fdividef( 1.0f, xadd( oma, 1.0e-15f ) ); // MUFU.RCP: gradients are not bit-exact anyway
 						const float dar = tcr - xsub( FR( j ), Pr[j] ) * inv;
 						const float dag = tcg - xsub( FG( j ), Pg[j] ) * inv;
 						const float dab = tcb - xsub( FB( j ), Pb[j] ) * inv;

@@ -14,11 +14,11 @@
 #include "gs2d_blend.cuh"
 
 #ifndef FWD_MINB
-#define FWD_MINB 1
+#define FWD_MINB 32   // P = 8 (one warp per tile): cap at 64 registers -> 32 resident warps per SM (measured best)
 #endif
 
 template <int P>
-__global__ void __launch_bounds__( BlendCfg<P>::NT, FWD_MINB ) k_forward( Geometry g, const SplatRec* __restrict__ rec,
+__global__ void __launch_bounds__( BlendCfg<P>::NT, P == 8 ? FWD_MINB : 1 ) k_forward( Geometry g, const SplatRec* __restrict__ rec,
                                                                 const unsigned* __restrict__ vals,
                                                                 const uint2* __restrict__ tile_range,
                                                                 const float4* __restrict__ target,
@@ -142,6 +142,7 @@ __global__ void __launch_bounds__( BlendCfg<P>::NT, FWD_MINB ) k_forward( Geomet
 				{
 					if( ( wd[j] & livemask[j] ) == 0u )
 						continue;
+					nlive += __popc( wd[j] & livemask[j] ); // warp-uniform count of the live pairs blended below
 					if( ( ( wd[j] >> lane ) & 1u ) && !( T[j] < min_T ) ) // covered (main.cpp:492-514) and live (:520)
 					{
 						const float vy = xsub( (float)( y0 + 2 * j ) + 0.5f, q0.y );
@@ -154,7 +155,6 @@ __global__ void __launch_bounds__( BlendCfg<P>::NT, FWD_MINB ) k_forward( Geomet
 						Cg[j] = xadd( Cg[j], xmul( xmul( T[j], q1.z ), alpha ) );
 						Cb[j] = xadd( Cb[j], xmul( xmul( T[j], q1.w ), alpha ) );
 						T[j] = xmul( T[j], xsub( 1.0f, alpha ) );                   // main.cpp:533
-						nlive++;
 					}
 					livemask[j] = __ballot_sync( 0xffffffffu, !( T[j] < min_T ) );
 				}
@@ -198,7 +198,6 @@ __global__ void __launch_bounds__( BlendCfg<P>::NT, FWD_MINB ) k_forward( Geomet
 	for( int o = 16; o > 0; o >>= 1 )
 	{
 		e += __shfl_xor_sync( 0xffffffffu, e, o );
-		nlive += __shfl_xor_sync( 0xffffffffu, nlive, o );
 	}
 	if( lane == 0 )
 	{
