@@ -335,6 +335,12 @@ class Fitter:
         self._ck(self.lib.gs2d_comm_init(self._ctx, rank, n_ranks, buf))
 
 
+def band_rows(tiles_y, rank, n_ranks):
+    """Tile rows [ty0, ty1) owned by `rank` — the same partition gs2d_comm_init / gs2d_set_band apply on the device."""
+    per = (tiles_y + n_ranks - 1) // n_ranks
+    return min(rank * per, tiles_y), min((rank + 1) * per, tiles_y)
+
+
 def comm_unique_id():
     buf = (C.c_uint8 * 128)()
     rc = load_library().gs2d_comm_unique_id(buf)

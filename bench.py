@@ -150,7 +150,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.perf_counter() - t_first,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -315,14 +315,27 @@ def run_ours(args):
         "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "last_mse": float(mse_last[0, 0]) if mse_last is not None else None,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     fit.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0
 
 
+def _emit(line):
+    """Print the ONE JSON line on the real stdout (fd 1 is pointed at stderr while the run is in progress so that
+    banners printed by native libraries, e.g. "NCCL version ...", cannot get in front of it)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)

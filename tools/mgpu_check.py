@@ -1,0 +1,46 @@
+#!/usr/bin/env python
+"""N-rank band-sharded fit vs the single-GPU fit (launch with torch.distributed.run, one process per GPU).
+Rank r fits tile-row band r with an NCCL all-reduce of the gradients; rank 0 then repeats the fit alone and compares."""
+import importlib, os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+gs2d = importlib.import_module("2dgaussiansplatting_b200")
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+W, H, N, ITERS = 700, 520, 6000, 12
+target = gs2d.synth_target(W, H, seed=3)
+box = [gs2d.comm_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(box, src=0)
+with gs2d.Fitter(W, H, N, device=local) as fit:
+    fit.comm_init(rank, world, box[0])
+    fit.set_target(target)
+    fit.restart()
+    mse_n = fit.step(ITERS)[:, 0]
+    s_n = fit.download()[0]
+    img_n = fit.image()
+ok = True
+if rank == 0:
+    with gs2d.Fitter(W, H, N, device=local) as fit:
+        fit.set_target(target)
+        fit.restart()
+        mse_1 = fit.step(ITERS)[:, 0]
+        s_1 = fit.download()[0]
+    rel = np.abs(mse_n - mse_1) / mse_1
+    d = np.abs(s_n.view(np.float32) - s_1.view(np.float32))
+    print(f"world={world} mse rel diff max {rel.max():.3e}; params |diff| q99 {np.quantile(d, 0.99):.3e} max {d.max():.3e}")
+    ok = rel.max() < 1e-4 and np.quantile(d, 0.99) < 1e-2
+# every rank must hold the same parameters after the all-reduced Adam
+t = torch.from_numpy(s_n.view(np.float32).copy()).cuda()
+tmin, tmax = t.clone(), t.clone()
+dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+same = bool((tmin == tmax).all())
+if rank == 0:
+    print("replicated parameters identical on all ranks:", same)
+dist.destroy_process_group()
+sys.exit(0 if (ok and same) else 1)
