@@ -45,7 +45,7 @@ ABI_SYMBOLS = [
     "gs2d_download_state", "gs2d_set_optimize_opacity", "gs2d_step", "gs2d_forward", "gs2d_backward", "gs2d_adam",
     "gs2d_download_image_rgba32f", "gs2d_download_grads", "gs2d_last_mse", "gs2d_get_stats", "gs2d_comm_unique_id",
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
-    "gs2d_set_profiling", "gs2d_get_profile",
+    "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
 ]
 
@@ -61,7 +61,7 @@ class Params(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("keys", C.c_uint64), ("live_pairs", C.c_uint64), ("staged", C.c_uint64), ("capacity", C.c_uint64),
                 ("live_pairs_sum", C.c_uint64), ("staged_sum", C.c_uint64), ("keys_sum", C.c_uint64),
-                ("n_forwards", C.c_uint64)]
+                ("n_forwards", C.c_uint64), ("live_pairs_backward", C.c_uint64)]
 
 
 class Gs2dError(RuntimeError):
@@ -112,6 +112,7 @@ def load_library():
     L.gs2d_last_step_ms.argtypes = [vp, C.POINTER(f)]
     L.gs2d_profile_step.argtypes = [vp, C.POINTER(f * 6)]
     L.gs2d_set_profiling.argtypes = [vp, i]
+    L.gs2d_set_stats.argtypes = [vp, i]
     L.gs2d_get_profile.argtypes = [vp, C.POINTER(C.c_double * 6), C.POINTER(C.c_longlong)]
     L.gs2d_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.gs2d_sync.argtypes = [vp]
@@ -309,6 +310,10 @@ class Fitter:
     def set_profiling(self, enable=True):
         """Bracket every iteration of step() with CUDA events on the library's stream (resets the sums)."""
         self._ck(self.lib.gs2d_set_profiling(self._ctx, int(bool(enable))))
+
+    def set_stats(self, enable=True):
+        """Work counters (live pairs, staged entries) of the forward blend launched by step(): on by default."""
+        self._ck(self.lib.gs2d_set_stats(self._ctx, int(bool(enable))))
 
     def get_profile(self):
         """-> ({group: mean ms per iteration}, iterations measured) since set_profiling()."""

@@ -10,6 +10,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
+#include <string>
 #include <vector>
 
 // ---- minimal NCCL surface, resolved at run time (only needed when gs2d_comm_init is called) --------------------
@@ -61,18 +63,16 @@ enum
 	NCCL_SUM = 0
 };
 
-int gs2d_pixels_per_thread( int which )
+int gs2d_tune( const char* env_name, int dflt )
 {
-	static int cached[2] = { 0, 0 };
-	if( !cached[which] )
-	{
-		const char* e = getenv( which ? "GS2D_PPT_BWD" : "GS2D_PPT_FWD" );
-		int v = e ? atoi( e ) : 0;
-		if( v != 1 && v != 2 && v != 4 && v != 8 )
-			v = which ? GS2D_PPT_BWD_DEFAULT : GS2D_PPT_FWD_DEFAULT;
-		cached[which] = v;
-	}
-	return cached[which];
+	static std::map<std::string, int> cache;
+	auto it = cache.find( env_name );
+	if( it != cache.end() )
+		return it->second;
+	const char* e = getenv( env_name );
+	const int v = e ? atoi( e ) : dflt;
+	cache[env_name] = v;
+	return v;
 }
 
 // ---- context ----------------------------------------------------------------------------------------------------
@@ -109,6 +109,8 @@ struct gs2d_ctx
 	std::vector<ProfRec> prof_pool;
 	size_t prof_used = 0;
 	bool profiling = false;
+	bool count_live = true;              // gs2d_set_stats: count live pairs / staged entries in the forward blend
+	unsigned long long bwd_live = 0;     // live pairs counted by the last gs2d_backward
 	double prof_sum[6] = { 0, 0, 0, 0, 0, 0 };
 	long long prof_iters = 0;
 };
@@ -333,7 +335,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.loss_partial, sizeof( double ) * (size_t)g.n_tiles_total ) );
-	CKC( cudaMalloc( &b.live_slots, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
+	CKC( cudaMalloc( &b.live_slots, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 3 ) );
 	b.staged_slots = b.live_slots + GS2D_LIVE_SLOTS;
 	CKC( cudaMalloc( &b.stats, sizeof( unsigned long long ) * 8 ) );
 	CKC( cudaMalloc( &b.loss, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
@@ -348,7 +350,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMemset( b.target, 0, sizeof( float4 ) * n_px ) );
 	CKC( cudaMemset( b.image, 0, sizeof( float4 ) * n_px ) );
 	CKC( cudaMemset( b.loss_partial, 0, sizeof( double ) * (size_t)g.n_tiles_total ) );
-	CKC( cudaMemset( b.live_slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2 ) );
+	CKC( cudaMemset( b.live_slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 3 ) );
 	CKC( cudaMemset( b.stats, 0, sizeof( unsigned long long ) * 8 ) );
 	CKC( cudaMemset( b.loss, 0, sizeof( double ) * ( (size_t)n_images + 1 ) ) );
 	DevState s0{};
@@ -534,7 +536,7 @@ extern "C" int gs2d_set_optimize_opacity( gs2d_ctx* c, int enabled )
 static int enqueue_forward( gs2d_ctx* c )
 {
 	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr );
-	c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->stream );
+	c->launches += launch_forward( c->g, c->b, c->sorted_buf, true, c->stream );
 	c->launches += launch_finalize_loss( c->g, c->b, c->stream );
 	c->have_forward = true;
 	return check_launch( c );
@@ -579,10 +581,10 @@ static int enqueue_iteration( gs2d_ctx* c )
 	PROF( 0 );
 	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr );
 	PROF( 2 );
-	c->launches += launch_forward( c->g, c->b, c->sorted_buf, s );
+	c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->count_live, s );
 	c->launches += launch_finalize_loss( c->g, c->b, s );
 	PROF( 3 );
-	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, s );
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s );
 	PROF( 4 );
 	int rc = enqueue_allreduce( c );
 	if( rc )
@@ -720,14 +722,20 @@ extern "C" int gs2d_backward( gs2d_ctx* c )
 		return GS2D_ERR_STATE;
 	CK( cudaSetDevice( c->device ) );
 	CK( cudaMemsetAsync( c->b.grads, 0, sizeof( float ) * (size_t)c->g.n_pad * GS2D_NPLANES, c->stream ) );
-	c->launches += launch_backward( c->g, c->b, c->sorted_buf, true, c->stream );
+	c->launches += launch_backward( c->g, c->b, c->sorted_buf, true, true, c->stream );
 	int rc = check_launch( c );
 	if( rc )
 		return rc;
 	rc = enqueue_allreduce( c );
 	if( rc )
 		return rc;
+	unsigned long long slots[GS2D_LIVE_SLOTS];
+	CK( cudaMemcpyAsync( slots, c->b.live_slots + 2 * GS2D_LIVE_SLOTS, sizeof( slots ), cudaMemcpyDeviceToHost,
+	                     c->stream ) );
 	CK( cudaStreamSynchronize( c->stream ) );
+	c->bwd_live = 0;
+	for( unsigned long long v : slots )
+		c->bwd_live += v;
 	return GS2D_OK;
 }
 
@@ -806,6 +814,7 @@ extern "C" int gs2d_get_stats( gs2d_ctx* c, gs2d_stats* out )
 	out->staged_sum = st[3];
 	out->keys_sum = st[4];
 	out->n_forwards = st[5];
+	out->live_pairs_backward = c->bwd_live;
 	return GS2D_OK;
 }
 
@@ -850,6 +859,14 @@ extern "C" int gs2d_set_profiling( gs2d_ctx* c, int enable )
 	for( double& v : c->prof_sum )
 		v = 0.0;
 	c->prof_iters = 0;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_set_stats( gs2d_ctx* c, int enable )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	c->count_live = enable != 0;
 	return GS2D_OK;
 }
 

@@ -16,12 +16,12 @@
 
 #include "../../include/gs2d.h"
 
-#define GS2D_TILE 16          // tile edge in pixels; one CTA of 256 threads per tile, one pixel per thread
+#define GS2D_TILE 16          // tile edge in pixels; one warp per tile, 8 pixels per lane (gs2d_blend.cuh)
 #define GS2D_BATCH 32         // list entries staged into shared memory per round
 #define GS2D_NPLANES 9
-#define GS2D_PPT_FWD_DEFAULT 8   // pixels per thread, forward blend (8 = one warp per tile)
-#define GS2D_PPT_BWD_DEFAULT 8   // pixels per thread, backward blend
 #define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
+#define GS2D_FWD_MINB_DEFAULT 24 // resident warps per SM the forward blend is register-capped for (env GS2D_FWD_MINB)
+#define GS2D_BWD_MINB_DEFAULT 20 // same for the backward blend (env GS2D_BWD_MINB)
 
 enum
 {
@@ -178,14 +178,15 @@ struct Buffers
 	DevState* state;
 };
 
-// pixels per thread of the blend kernels: which = 0 forward, 1 backward (env GS2D_PPT_FWD / GS2D_PPT_BWD override)
-int gs2d_pixels_per_thread( int which );
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
                                cudaEvent_t after_emit );
-int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, cudaStream_t s );
-int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, cudaStream_t s );
+// developer tuning knob: integer environment variable read once per name, else the default
+int gs2d_tune( const char* env_name, int dflt );
+int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s );
+int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, bool count_live,
+                     cudaStream_t s );
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
 int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );

@@ -88,6 +88,7 @@ typedef struct gs2d_stats
 	uint64_t staged_sum;
 	uint64_t keys_sum;
 	uint64_t n_forwards;
+	uint64_t live_pairs_backward; /* live pairs counted by the last gs2d_backward (same set => same count) */
 } gs2d_stats;
 
 typedef struct gs2d_ctx gs2d_ctx;
@@ -155,6 +156,9 @@ int gs2d_profile_step( gs2d_ctx* ctx, float out_ms[6] );
  * (same order as gs2d_profile_step) and the number of iterations measured. gs2d_set_profiling resets the sums. */
 int gs2d_set_profiling( gs2d_ctx* ctx, int enable );
 int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
+/* Work counters on/off (default on): while off, the forward blend launched by gs2d_step does not count live pairs
+ * (one instruction per 8x4 block visit); gs2d_forward / gs2d_backward always count. */
+int gs2d_set_stats( gs2d_ctx* ctx, int enable );
 /* Number of kernel launches the library has issued on this context so far. */
 int gs2d_launch_count( gs2d_ctx* ctx, uint64_t* n );
 

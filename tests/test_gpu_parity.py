@@ -92,6 +92,7 @@ def test_forward_backward_reference_jpegs(golden_dir, cfg):
         stats = fit.stats()
         fit.backward()
         g = fit.grads()
+        assert fit.stats()["live_pairs_backward"] == stats["live_pairs"]  # both passes walk the same live set
     splats = ob.init_splats(W, H, 1024)
     img_cpu, visited, live = ob.forward(W, H, splats)
     exact, d = assert_image_close(img, img_cpu)

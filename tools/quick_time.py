@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Quick per-kernel-group timing of the fit iteration (developer tool; the judged numbers come from bench.py).
-usage: [GS2D_PPT_FWD=..] [GS2D_PPT_BWD=..] python tools/quick_time.py [size] [splats] [iters] [n_images]"""
+usage: [GS2D_FWD_MINB=..] [GS2D_BWD_MINB=..] [GS2D_STATS=0] python tools/quick_time.py [size] [splats] [iters] [n_images]"""
 import importlib, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -17,12 +17,13 @@ with gs2d.Fitter(S, S, N, n_images=B) as fit:
     fit.restart()
     fit.step(3)
     fit.set_profiling(True)
+    fit.set_stats(os.environ.get('GS2D_STATS', '1') != '0')
     fit.step(K, want_mse=False)
     fit.sync()
     ms = fit.last_step_ms() / K
     prof, n = fit.get_profile()
     st = fit.stats()
-    print(f"PPT fwd={os.environ.get('GS2D_PPT_FWD','-')} bwd={os.environ.get('GS2D_PPT_BWD','-')} {S}x{S} N={N} B={B}: "
+    print(f"MINB fwd={os.environ.get('GS2D_FWD_MINB','-')} bwd={os.environ.get('GS2D_BWD_MINB','-')} stats={os.environ.get('GS2D_STATS','1')} {S}x{S} N={N} B={B}: "
           f"{ms:.3f} ms/it ({1e3/ms:.1f} it/s) | " + " ".join(f"{k}={v:.3f}" for k, v in prof.items()) +
           f" | keys/it={st['keys_sum']/max(st['n_forwards'],1):.3e} live/it={st['live_pairs_sum']/max(st['n_forwards'],1):.3e}"
           f" staged/it={st['staged_sum']/max(st['n_forwards'],1):.3e}")
