@@ -206,12 +206,16 @@ static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
 	if( b.radix_hist )
 		cudaFree( b.radix_hist );
 	b.radix_hist = nullptr;
+	if( b.cover )
+		cudaFree( b.cover );
+	b.cover = nullptr;
 	capacity = std::min<unsigned long long>( std::max<unsigned long long>( capacity, 1ull << 16 ), 0xFFFF0000ull );
 	for( int i = 0; i < 2; i++ )
 	{
 		CK( cudaMalloc( &b.keys[i], sizeof( unsigned ) * capacity ) );
 		CK( cudaMalloc( &b.vals[i], sizeof( unsigned ) * capacity ) );
 	}
+	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * 8 * capacity ) );
 	b.capacity = capacity;
 	b.max_chunks = (unsigned)( ( capacity + 4095 ) / 4096 );
 	const size_t hist_n = 256ull * b.max_chunks;
@@ -239,7 +243,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.rect,  b.cnt,
-	                 b.scan_tmp,   b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.radix_hist, b.tile_range,
+	                 b.scan_tmp,   b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.radix_hist, b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage };
 	for( void* p : ptrs )

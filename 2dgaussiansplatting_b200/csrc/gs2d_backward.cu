@@ -52,19 +52,33 @@ __device__ __forceinline__ float warp_reduce8( const float v[8], int lane )
 
 // MINB = resident warps (tiles) per SM the register allocation is capped for: 20 -> 96 registers, 16 -> 128.
 // COUNT: also count the live (pixel, splat) pairs into live_slots (same set as the forward pass).
+// lane k gathers the 8 coverage words the forward pass stored for list position base + k
+__device__ __forceinline__ void gather_cover( TileSmem<2>& sm, int stage, int lane, const unsigned* __restrict__ cover,
+                                              unsigned base, bool valid )
+{
+	if( valid )
+	{
+		const uint4* src = reinterpret_cast<const uint4*>( cover + ( (size_t)base + lane ) * 8 );
+		uint4* dst = reinterpret_cast<uint4*>( &sm.words[stage][lane][0] );
+		cp_async16( dst, src );
+		cp_async16( dst + 1, src + 1 );
+	}
+}
+
 template <int MINB, bool OPACITY, bool COUNT>
 __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
                                                               const unsigned* __restrict__ vals,
                                                               const uint2* __restrict__ tile_range,
                                                               const float4* __restrict__ target,
                                                               const float4* __restrict__ image,
+                                                              const unsigned* __restrict__ cover,
                                                               float* __restrict__ grads,
                                                               unsigned long long* __restrict__ live_slots,
                                                               const DevState* __restrict__ st )
 {
 	if( st->need_capacity )
 		return;
-	__shared__ TileSmem sm;
+	__shared__ TileSmem<2> sm;
 	__shared__ __align__( 16 ) float part[GS2D_BATCH][OPACITY ? 12 : 8]; // per-entry totals: 3 colour sums, 5 moments (, opacity)
 
 	const int lane = threadIdx.x;
@@ -114,6 +128,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		const bool v = start + lane < end;
 		idx_cur = v ? vals[start + lane] : 0u;
 		gather_record<4>( sm, 0, lane, rec, idx_cur, v );
+		gather_cover( sm, 0, lane, cover, start, v );
 		cp_async_commit();
 	}
 	unsigned idx_nxt = ( start + GS2D_BATCH + lane < end ) ? vals[start + GS2D_BATCH + lane] : 0u;
@@ -127,6 +142,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		if( nbase < end )
 		{
 			gather_record<4>( sm, stage ^ 1, lane, rec, idx_nxt, nbase + lane < end );
+			gather_cover( sm, stage ^ 1, lane, cover, nbase, nbase + lane < end );
 			cp_async_commit();
 			idx_cur = idx_nxt;
 			idx_nxt = ( nbase + GS2D_BATCH + lane < end ) ? vals[nbase + GS2D_BATCH + lane] : 0u;
@@ -135,8 +151,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		else
 			cp_async_wait<0>();
 		__syncwarp();
-		unsigned ent = solve_batch( sm, stage, nb, lane, tile_x0, tile_y0, g.W, g.H );
-		__syncwarp();
+		uint4 cwa, cwb;
+		unsigned ent = touching_entries( sm, stage, nb, lane, cwa, cwb );
 
 		unsigned visited = 0;
 #pragma unroll 1
@@ -144,8 +160,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		{
 			const int k = __ffs( ent ) - 1;
 			ent &= ent - 1u;
-			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[k][0] );
-			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[k][4] );
+			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[stage][k][0] );
+			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[stage][k][4] );
 			const unsigned wd[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
 			unsigned hit = 0;
 #pragma unroll
@@ -290,7 +306,7 @@ int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool w
 		cudaMemsetAsync( slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS, s );
 #define LAUNCH_BWD3( MINB, OP, CNT )                                                                                  \
 	k_backward<MINB, OP, CNT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image,     \
-	                                               b.grads, slots, b.state )
+	                                               b.cover, b.grads, slots, b.state )
 #define LAUNCH_BWD( MINB )                                                                                            \
 	do                                                                                                                \
 	{                                                                                                                 \

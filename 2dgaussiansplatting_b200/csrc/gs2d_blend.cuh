@@ -14,15 +14,17 @@
 #pragma once
 #include "gs2d_internal.cuh"
 
+// WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)
+template <int WSTAGES>
 struct TileSmem
 {
-	SplatRec rec[2][GS2D_BATCH];        // 4 KB, double-buffered records of the staged list entries
-	unsigned words[GS2D_BATCH][8];      // 1 KB, exact coverage: word j of entry k = 8x4 block j (bit = lane)
+	SplatRec rec[2][GS2D_BATCH];              // 4 KB, double-buffered records of the staged list entries
+	unsigned words[WSTAGES][GS2D_BATCH][8];   // 1 KB each, exact coverage: word j of entry k = 8x4 block j (bit = lane)
 };
 
 // lane k gathers QUADS float4 of record idx into sm.rec[stage][k]
-template <int QUADS>
-__device__ __forceinline__ void gather_record( TileSmem& sm, int stage, int lane, const SplatRec* __restrict__ rec,
+template <int QUADS, int WSTAGES>
+__device__ __forceinline__ void gather_record( TileSmem<WSTAGES>& sm, int stage, int lane, const SplatRec* __restrict__ rec,
                                                unsigned idx, bool valid )
 {
 	if( valid )
@@ -36,31 +38,38 @@ __device__ __forceinline__ void gather_record( TileSmem& sm, int stage, int lane
 }
 
 // Exact footprint of the nb staged entries of `stage`: 16 rows x nb entries = up to 512 solves, 16 per lane.
-// Lane (h = lane >> 4, r = lane & 15) solves row r of entries 2i + h. Returns the mask of entries that cover at
-// least one pixel of the tile (entries outside it are never looked at again).
-__device__ __forceinline__ unsigned solve_batch( TileSmem& sm, int stage, int nb, int lane, int tile_x0, int tile_y0,
-                                                 int W, int H )
+// Lane (h = lane >> 4, r = lane & 15) solves row r of entries 2i + h and scatters the 16-bit row mask as two bytes
+// into the block words of the entry.
+__device__ __forceinline__ void solve_batch( TileSmem<1>& sm, int stage, int nb, int lane, int tile_x0, int tile_y0,
+                                             int W, int H )
 {
 	const int h = lane >> 4, r = lane & 15;
 	const int y = tile_y0 + r;
-	const int boff = ( r >> 2 ) * 8 + ( r & 3 ); // byte (r & 3) of word 2*(r >> 2); the right half is 4 bytes on
-	unsigned ent = 0;
+	// byte (r & 3) of word 2*(r >> 2) of entry h; the right half of the row is 4 bytes on, the next entry pair 64
+	unsigned char* wb = reinterpret_cast<unsigned char*>( &sm.words[0][h][0] ) + ( r >> 2 ) * 8 + ( r & 3 );
+	const SplatRec* s = &sm.rec[stage][h];
 #pragma unroll 2
-	for( int i = 0; 2 * i < nb; i++ )
+	for( int k = h; k < nb; k += 2, s += 2, wb += 64 )
 	{
-		const int k = 2 * i + h;
-		unsigned m = 0;
-		if( k < nb )
-		{
-			const SplatRec& s = sm.rec[stage][k];
-			m = row_mask( s.px, s.py, s.a, s.b, s.d, s.begY, s.endY, y, tile_x0, W, H );
-			unsigned char* wb = reinterpret_cast<unsigned char*>( &sm.words[k][0] ) + boff;
-			wb[0] = (unsigned char)( m & 0xffu );
-			wb[4] = (unsigned char)( m >> 8 );
-		}
-		const unsigned bal = __ballot_sync( 0xffffffffu, m != 0u );
-		ent |= ( ( bal & 0xffffu ) ? 1u : 0u ) << ( 2 * i );
-		ent |= ( ( bal >> 16 ) ? 2u : 0u ) << ( 2 * i );
+		const unsigned m = row_mask( s->px, s->py, s->a, s->b, s->d, s->begY, s->endY, y, tile_x0, W, H );
+		wb[0] = (unsigned char)( m & 0xffu );
+		wb[4] = (unsigned char)( m >> 8 );
 	}
-	return ent;
+}
+
+// Mask of the staged entries that cover at least one pixel of the tile (the others are never looked at again);
+// lane k owns entry k. wa/wb return the lane's own 8 coverage words.
+template <int WSTAGES>
+__device__ __forceinline__ unsigned touching_entries( const TileSmem<WSTAGES>& sm, int wstage, int nb, int lane,
+                                                      uint4& wa, uint4& wb )
+{
+	wa = make_uint4( 0u, 0u, 0u, 0u );
+	wb = wa;
+	if( lane < nb )
+	{
+		wa = *reinterpret_cast<const uint4*>( &sm.words[wstage][lane][0] );
+		wb = *reinterpret_cast<const uint4*>( &sm.words[wstage][lane][4] );
+	}
+	const unsigned any = wa.x | wa.y | wa.z | wa.w | wb.x | wb.y | wb.z | wb.w;
+	return __ballot_sync( 0xffffffffu, any != 0u );
 }

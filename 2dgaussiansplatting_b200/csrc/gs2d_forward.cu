@@ -22,6 +22,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
                                                              const uint2* __restrict__ tile_range,
                                                              const float4* __restrict__ target,
                                                              float4* __restrict__ image,
+                                                             unsigned* __restrict__ cover,
                                                              double* __restrict__ loss_partial,
                                                              unsigned long long* __restrict__ live_slots,
                                                              unsigned long long* __restrict__ staged_slots,
@@ -29,7 +30,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 {
 	if( st->need_capacity )
 		return;
-	__shared__ TileSmem sm;
+	__shared__ TileSmem<1> sm;
 
 	const int lane = threadIdx.x;
 	const int tile_x = blockIdx.x, tile_y = blockIdx.y + g.band_ty0, img = blockIdx.z;
@@ -81,17 +82,26 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 		else
 			cp_async_wait<0>();
 		__syncwarp();
-		unsigned ent = solve_batch( sm, stage, nb, lane, tile_x0, tile_y0, g.W, g.H );
+		solve_batch( sm, stage, nb, lane, tile_x0, tile_y0, g.W, g.H );
 		__syncwarp();
 		nstaged += nb;
+		// the coverage words go to HBM for the backward pass (32 bytes per staged entry, coalesced)
+		uint4 cwa, cwb;
+		unsigned ent = touching_entries( sm, 0, nb, lane, cwa, cwb );
+		if( lane < nb )
+		{
+			uint4* dst = reinterpret_cast<uint4*>( cover + ( (size_t)base + lane ) * 8 );
+			__stcg( dst, cwa );
+			__stcg( dst + 1, cwb );
+		}
 
 #pragma unroll 1
 		while( ent )
 		{
 			const int k = __ffs( ent ) - 1;
 			ent &= ent - 1u;
-			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[k][0] );
-			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[k][4] );
+			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[0][k][0] );
+			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[0][k][4] );
 			const unsigned wd[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
 			unsigned hit = 0;
 #pragma unroll
@@ -185,10 +195,10 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 	{                                                                                                                 \
 		if( count_live )                                                                                              \
 			k_forward<MINB, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image, \
-			                                           b.loss_partial, b.live_slots, b.staged_slots, b.state );       \
+			                                           b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state );       \
 		else                                                                                                          \
 			k_forward<MINB, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,         \
-			                                            b.image, b.loss_partial, b.live_slots, b.staged_slots,        \
+			                                            b.image, b.cover, b.loss_partial, b.live_slots, b.staged_slots,        \
 			                                            b.state );                                                    \
 	} while( 0 )
 	switch( gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) )

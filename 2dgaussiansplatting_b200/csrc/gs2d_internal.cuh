@@ -162,6 +162,7 @@ struct Buffers
 	unsigned long long* scan_tmp;
 	unsigned* keys[2];
 	unsigned* vals[2];
+	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward)
 	unsigned long long capacity;
 	unsigned* radix_hist;     // [256][max_chunks]
 	unsigned max_chunks;
