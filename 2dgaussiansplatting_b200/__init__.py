@@ -45,7 +45,7 @@ ABI_SYMBOLS = [
     "gs2d_download_state", "gs2d_set_optimize_opacity", "gs2d_step", "gs2d_forward", "gs2d_backward", "gs2d_adam",
     "gs2d_download_image_rgba32f", "gs2d_download_grads", "gs2d_last_mse", "gs2d_get_stats", "gs2d_comm_unique_id",
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
-    "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats",
+    "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
 ]
 
@@ -113,6 +113,7 @@ def load_library():
     L.gs2d_profile_step.argtypes = [vp, C.POINTER(f * 6)]
     L.gs2d_set_profiling.argtypes = [vp, i]
     L.gs2d_set_stats.argtypes = [vp, i]
+    L.gs2d_set_tuning.argtypes = [C.c_char_p, i]
     L.gs2d_get_profile.argtypes = [vp, C.POINTER(C.c_double * 6), C.POINTER(C.c_longlong)]
     L.gs2d_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.gs2d_sync.argtypes = [vp]
@@ -338,6 +339,13 @@ class Fitter:
     def comm_init(self, rank, n_ranks, unique_id):
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
         self._ck(self.lib.gs2d_comm_init(self._ctx, rank, n_ranks, buf))
+
+
+def set_tuning(name, value):
+    """Developer knob of the native library (process-wide), e.g. set_tuning("GS2D_CULL", 0)."""
+    rc = load_library().gs2d_set_tuning(name.encode(), int(value))
+    if rc:
+        raise Gs2dError(rc, "gs2d_set_tuning")
 
 
 def band_rows(tiles_y, rank, n_ranks):

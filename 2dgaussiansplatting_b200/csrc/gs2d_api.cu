@@ -63,9 +63,14 @@ enum
 	NCCL_SUM = 0
 };
 
-int gs2d_tune( const char* env_name, int dflt )
+static std::map<std::string, int>& tune_cache()
 {
 	static std::map<std::string, int> cache;
+	return cache;
+}
+int gs2d_tune( const char* env_name, int dflt )
+{
+	auto& cache = tune_cache();
 	auto it = cache.find( env_name );
 	if( it != cache.end() )
 		return it->second;
@@ -73,6 +78,13 @@ int gs2d_tune( const char* env_name, int dflt )
 	const int v = e ? atoi( e ) : dflt;
 	cache[env_name] = v;
 	return v;
+}
+extern "C" int gs2d_set_tuning( const char* name, int value )
+{
+	if( !name )
+		return GS2D_ERR_INVALID;
+	tune_cache()[name] = value;
+	return GS2D_OK;
 }
 
 // ---- context ----------------------------------------------------------------------------------------------------
@@ -203,23 +215,15 @@ static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
 			cudaFree( b.vals[i] );
 		b.keys[i] = b.vals[i] = nullptr;
 	}
-	if( b.radix_hist )
-		cudaFree( b.radix_hist );
-	b.radix_hist = nullptr;
 	if( b.cover )
 		cudaFree( b.cover );
 	b.cover = nullptr;
 	capacity = std::min<unsigned long long>( std::max<unsigned long long>( capacity, 1ull << 16 ), 0xFFFF0000ull );
-	for( int i = 0; i < 2; i++ )
-	{
-		CK( cudaMalloc( &b.keys[i], sizeof( unsigned ) * capacity ) );
-		CK( cudaMalloc( &b.vals[i], sizeof( unsigned ) * capacity ) );
-	}
+	CK( cudaMalloc( &b.keys[0], sizeof( unsigned ) * capacity ) );
+	CK( cudaMalloc( &b.vals[0], sizeof( unsigned ) * capacity ) );
+	CK( cudaMalloc( &b.vals[1], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * 8 * capacity ) );
 	b.capacity = capacity;
-	b.max_chunks = (unsigned)( ( capacity + 4095 ) / 4096 );
-	const size_t hist_n = 256ull * b.max_chunks;
-	CK( cudaMalloc( &b.radix_hist, sizeof( unsigned ) * ( hist_n + hist_n / 1024 + 16 ) ) );
 	return GS2D_OK;
 }
 
@@ -242,8 +246,8 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->comm && g_nccl.CommDestroy )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
-	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.rect,  b.cnt,
-	                 b.scan_tmp,   b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.radix_hist, b.cover, b.tile_range,
+	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.tile_cnt, b.tile_cur,
+	                 b.scan_sums,  b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage };
 	for( void* p : ptrs )
@@ -332,9 +336,9 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.adam_m, plane_bytes ) );
 	CKC( cudaMalloc( &b.adam_v, plane_bytes ) );
 	CKC( cudaMalloc( &b.rec, sizeof( SplatRec ) * (size_t)std::max( g.n_total, 1 ) ) );
-	CKC( cudaMalloc( &b.rect, sizeof( ushort4 ) * (size_t)std::max( g.n_total, 1 ) ) );
-	CKC( cudaMalloc( &b.cnt, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
-	CKC( cudaMalloc( &b.scan_tmp, sizeof( unsigned long long ) * ( 2 * (size_t)nb + 16 ) ) );
+	CKC( cudaMalloc( &b.tile_cnt, sizeof( unsigned ) * ( (size_t)g.n_tiles_total + 4 ) ) );
+	CKC( cudaMalloc( &b.tile_cur, sizeof( unsigned ) * ( (size_t)g.n_tiles_total + 4 ) ) );
+	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( (size_t)g.n_tiles_total / 1024 + 16 ) ) );
 	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );

@@ -1,35 +1,100 @@
-// gs2d_binning.cu — per-Gaussian preprocessing, tile binning and the on-device radix sort.
+// gs2d_binning.cu — per-Gaussian preprocessing and tile binning.
 //
 // Replaces, for a pixel-parallel GPU pass, what the reference does implicitly by iterating splats in index order
 // and scan-converting each one (main.cpp:419-538): here every 16x16 tile gets the list of splats whose footprint
 // may touch it, ordered by splat index (== the reference's blend order).
 //
-//   k_preprocess   : covariance, inverse, row range (cov_of main.cpp:206-221, :432-436, :489-491), conservative tile
-//                    rectangle, per-splat tile count + block-local exclusive scan of the counts
-//   k_scan_top     : scan of the block sums, total key count, capacity check
-//   k_emit         : duplicated (tile | splat) keys, written in ascending splat order
-//   k_radix_*      : stable LSD radix passes over the TILE bits only (8 bits per pass). Because the emission is
-//                    already ordered by splat index and every pass is stable, the result is ordered by
-//                    (tile, splat index) after ceil(log2(tiles)/8) passes instead of the ~5 a full 64-bit key needs.
-//   k_tile_ranges  : [start,end) of every tile's list
+// The (tile | order) keys are sorted MSD-first, and the first digit is the whole tile id:
+//   k_preprocess   : covariance, inverse, row range (cov_of main.cpp:206-221, :432-436, :489-491) -> 64-byte record;
+//                    the tiles the 3-sigma ellipse can touch (per tile row: the x-extent of the ellipse inside the
+//                    band of that row's pixel centres, see tile_span) are counted per tile (red.add) and written as
+//                    unordered (tile, splat) pairs
+//   k_scan_*       : exclusive scan of the tile counts = bucket offsets; total key count and the capacity check
+//   k_bucket       : one thread per pair: slot = atomicAdd( cursor[tile], 1 ) -> the splat index lands in its tile's
+//                    bucket (arbitrary order inside the bucket)
+//   k_tile_sort    : one CTA per tile sorts its bucket by splat index in shared memory (normalised bitonic network,
+//                    virtual +inf padding; buckets beyond the shared-memory size are sorted in place in HBM) and
+//                    writes the tile's [start,end)
+// Splat indices are unique inside a bucket, so the sorted lists — and everything downstream — are deterministic
+// although the bucket pass uses atomics.
 #include "gs2d_internal.cuh"
 
-#define RADIX_BITS 8
-#define RADIX_BINS 256
-#define RADIX_THREADS 256
-#define RADIX_ITEMS 16
-#define RADIX_CHUNK ( RADIX_THREADS * RADIX_ITEMS )
-
 #define PRE_THREADS 256
+#define SORT_THREADS 128
+#define SORT_SMEM_MAX 4096   // bucket entries sorted in shared memory (16 KB); longer buckets are sorted in HBM
+
+// Conservative column span [tx_lo, tx_hi] of the tiles of tile row ty that the splat's footprint can touch.
+// The reference covers pixel (x, y) iff begY <= y <= endY and x in [(int)(px+u0), (int)(px+u1)], u0/u1 the chord of the
+// ellipse q(v) = a vx^2 + 2 b vx vy + d vy^2 <= 9 at the row centre vy = y + 0.5 - py (main.cpp:489-509). (int)
+// moves an end by less than one pixel, so a tile [X0, X0+16) can only be touched if the x-extent [min u0, max u1] of
+// the ellipse inside the band of this tile row's pixel centres reaches (X0 - 1, X0 + 16). The ellipse is convex:
+// max u1 over the band is the ellipse's rightmost point if that lies in the band, else it is at a band end.
+// Returns false if no row of the tile row is inside [begY, endY].
+struct SpanConsts
+{
+	float px, py, a, b, d;
+	float inv_a;    // 1 / a
+	float vx_max;   // 3 * sqrt( d / (a d - b^2) ): half width of the ellipse
+	float vy_at;    // vy of the rightmost point: -b * vx_max / d   (leftmost: -vy_at)
+	float delta;    // slack for float error of everything here and of the reference's own float chord solve
+	int begY, endY;
+};
+
+__device__ __forceinline__ bool tile_span( const SpanConsts& k, int ty, int H, int rtx0, int rtx1, int& tx_lo,
+                                           int& tx_hi )
+{
+	const int Y0 = ty * GS2D_TILE;
+	const int ylo = max( max( Y0, k.begY ), 0 ), yhi = min( min( Y0 + GS2D_TILE - 1, k.endY ), H - 1 );
+	if( ylo > yhi )
+		return false;
+	const float lo = ( (float)ylo + 0.5f - k.py ) - k.delta, hi = ( (float)yhi + 0.5f - k.py ) + k.delta;
+	// chord ends at the two band ends
+	const float bl = k.b * lo, bh = k.b * hi;
+	const float sl = sqrtf( fmaxf( bl * bl - k.a * ( k.d * lo * lo - 9.0f ), 0.0f ) );
+	const float sh = sqrtf( fmaxf( bh * bh - k.a * ( k.d * hi * hi - 9.0f ), 0.0f ) );
+	float umax = fmaxf( ( -bl + sl ) * k.inv_a, ( -bh + sh ) * k.inv_a );
+	float umin = fminf( ( -bl - sl ) * k.inv_a, ( -bh - sh ) * k.inv_a );
+	if( lo <= k.vy_at && k.vy_at <= hi )
+		umax = k.vx_max;
+	if( lo <= -k.vy_at && -k.vy_at <= hi )
+		umin = -k.vx_max;
+	const float E = k.px + umin - k.delta;         // a tile needs X0 + 16 > E
+	const float F = k.px + umax + 1.0f + k.delta;  // and X0 < F
+	// NaN anywhere -> fmaxf/fminf return the rectangle bound: the conservative rectangle is the fallback
+	tx_lo = (int)fmaxf( floorf( E * ( 1.0f / GS2D_TILE ) ), (float)rtx0 );
+	tx_hi = (int)fminf( floorf( F * ( 1.0f / GS2D_TILE ) ), (float)rtx1 );
+	return tx_lo <= tx_hi;
+}
 
 // ------------------------------------------------------------------------------------------------ preprocess ---
+// Per-splat part: record + span constants + conservative tile rectangle (tile units; empty if rtx0 > rtx1).
+struct SplatBin
+{
+	SpanConsts k;
+	int rtx0, rtx1, ty0, ty1;
+	int tile_base; // first tile id of the splat's image
+};
+
+#define BIG_RECT 1024 // rectangles with more tiles than this are binned by the whole warp
+
 __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const float* __restrict__ params,
-                                                               SplatRec* __restrict__ rec, ushort4* __restrict__ rect,
-                                                               unsigned* __restrict__ cnt_local,
-                                                               unsigned* __restrict__ block_sum )
+                                                               SplatRec* __restrict__ rec,
+                                                               unsigned* __restrict__ tile_cnt,
+                                                               unsigned* __restrict__ pair_tile,
+                                                               unsigned* __restrict__ pair_splat,
+                                                               unsigned long long capacity, int cull,
+                                                               DevState* __restrict__ st )
 {
 	const int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
-	unsigned cnt = 0;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	SplatBin sb;
+	sb.rtx0 = 1;
+	sb.rtx1 = 0;
+	sb.ty0 = 1;
+	sb.ty1 = 0;
+	sb.tile_base = 0;
+	sb.k.begY = 1;
+	sb.k.endY = 0;
 	if( gi < g.n_total )
 	{
 		const float px = params[PL_PX * g.n_pad + gi];
@@ -88,33 +153,52 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		// Conservative tile rectangle. Rows: exactly the reference's [begY, endY]. Columns: every chord of the 3-sigma
 		// ellipse lies within pos.x +- 3*sqrt(cov[0][0]) = 3*sqrt(d*det); widened by 2 px + 1e-4 relative for the
 		// truncation rule and the float error of the quadratic solve. Only a superset is needed here: the exact
-		// per-pixel set is decided by row_mask() in the blend kernels.
+		// per-pixel set is decided by row_mask() in the forward blend.
 		const int H = g.H, W = g.W;
-		int y0 = max( begY, 0 ), y1 = min( endY, H - 1 );
-		float hx = xmul( xsqrt( xmul( d, det ) ), 3.0f );
-		float m = 2.0f + hx * 1.0e-4f;
-		float fx0 = floorf( px - hx - m ), fx1 = floorf( px + hx + m );
-		int x0 = ( fx0 == fx0 ) ? (int)fmaxf( fx0, 0.0f ) : 0;
+		const int y0 = max( begY, 0 ), y1 = min( endY, H - 1 );
+		const float hx = xmul( xsqrt( xmul( d, det ) ), 3.0f );
+		const float m = 2.0f + hx * 1.0e-4f;
+		const float fx0 = floorf( px - hx - m ), fx1 = floorf( px + hx + m );
+		const int x0 = ( fx0 == fx0 ) ? (int)fmaxf( fx0, 0.0f ) : 0;
 		int x1 = ( fx1 == fx1 ) ? (int)fminf( fx1, (float)( W - 1 ) ) : W - 1;
 		if( fx1 < 0.0f )
 			x1 = -1;
-		ushort4 rc = make_ushort4( 1, 1, 0, 0 ); // empty rectangle (width 0)
 		if( y0 <= y1 && x0 <= x1 )
 		{
-			int ty0 = max( y0 / GS2D_TILE, g.band_ty0 ), ty1 = min( y1 / GS2D_TILE, g.band_ty1 - 1 );
-			int tx0 = x0 / GS2D_TILE, tx1 = x1 / GS2D_TILE;
-			if( ty0 <= ty1 )
-			{
-				cnt = (unsigned)( ( ty1 - ty0 + 1 ) * ( tx1 - tx0 + 1 ) );
-				rc = make_ushort4( (unsigned short)tx0, (unsigned short)ty0, (unsigned short)tx1, (unsigned short)ty1 );
-			}
+			sb.ty0 = max( y0 / GS2D_TILE, g.band_ty0 );
+			sb.ty1 = min( y1 / GS2D_TILE, g.band_ty1 - 1 );
+			sb.rtx0 = x0 / GS2D_TILE;
+			sb.rtx1 = x1 / GS2D_TILE;
 		}
-		rect[gi] = rc;
+		sb.tile_base = ( gi / g.n_splats ) * g.tiles_y * g.tiles_x;
+		sb.k.px = px;
+		sb.k.py = py;
+		sb.k.a = a;
+		sb.k.b = b;
+		sb.k.d = d;
+		sb.k.inv_a = 1.0f / a;
+		sb.k.vx_max = hx; // 3 * sqrt( cov[0][0] ) == 3 * sqrt( d / (a d - b^2) )
+		sb.k.vy_at = -b * hx / d;
+		sb.k.delta = cull ? 0.02f + 1.0e-3f * hx + 1.0e-6f * fabsf( px ) : __int_as_float( 0x7fc00000 ); // NaN: no culling
+		sb.k.begY = begY;
+		sb.k.endY = endY;
 	}
+	const bool has = sb.ty0 <= sb.ty1 && sb.rtx0 <= sb.rtx1;
+	const bool big = has && (long long)( sb.ty1 - sb.ty0 + 1 ) * ( sb.rtx1 - sb.rtx0 + 1 ) > BIG_RECT;
 
-	// block-local exclusive scan of cnt (warp shuffles, then the 8 warp totals)
+	// phase A: number of pairs of this splat (small rectangles only)
+	unsigned cnt = 0;
+	if( has && !big )
+		for( int ty = sb.ty0; ty <= sb.ty1; ty++ )
+		{
+			int lo, hi;
+			if( tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
+				cnt += (unsigned)( hi - lo + 1 );
+		}
+
+	// block-exclusive scan of cnt, one reservation in the pair list per block
 	__shared__ unsigned warp_tot[PRE_THREADS / 32];
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	__shared__ unsigned long long block_base;
 	unsigned incl = cnt;
 #pragma unroll
 	for( int o = 1; o < 32; o <<= 1 )
@@ -135,132 +219,71 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			wbase += t;
 		total += t;
 	}
-	if( gi < g.n_total )
-		cnt_local[gi] = wbase + incl - cnt; // exclusive, block-local
 	if( threadIdx.x == 0 )
-		block_sum[blockIdx.x] = total;
-}
-
-// One block: exclusive scan of the block sums (u64 accumulation), total, capacity check.
-__global__ void __launch_bounds__( 1024 ) k_scan_top( const unsigned* __restrict__ block_sum, int nb,
-                                                      unsigned long long* __restrict__ block_base,
-                                                      unsigned long long capacity, DevState* st )
-{
-	__shared__ unsigned long long wtot[32];
-	__shared__ unsigned long long carry_s;
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	if( threadIdx.x == 0 )
-		carry_s = 0;
+		block_base = total ? atomicAdd( &st->n_keys, (unsigned long long)total ) : 0ull;
 	__syncthreads();
-	for( int base = 0; base < nb; base += 1024 )
+
+	// phase B: write the pairs and count them per tile
+	if( cnt && block_base + total <= capacity )
 	{
-		int i = base + threadIdx.x;
-		unsigned long long v = ( i < nb ) ? block_sum[i] : 0ull, incl = v;
+		unsigned long long pos = block_base + wbase + incl - cnt;
+		for( int ty = sb.ty0; ty <= sb.ty1; ty++ )
+		{
+			int lo, hi;
+			if( !tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
+				continue;
+			const unsigned row = (unsigned)( sb.tile_base + ty * g.tiles_x );
+			for( int tx = lo; tx <= hi; tx++, pos++ )
+			{
+				pair_tile[pos] = row + (unsigned)tx;
+				pair_splat[pos] = (unsigned)gi;
+				atomicAdd( &tile_cnt[row + (unsigned)tx], 1u );
+			}
+		}
+	}
+
+	// phase C: big rectangles, one splat at a time by the whole warp: lanes take tile rows, each row reserves its own
+	// run of the pair list
+	unsigned bigs = __ballot_sync( 0xffffffffu, big );
+	while( bigs )
+	{
+		const int j = __ffs( bigs ) - 1;
+		bigs &= bigs - 1u;
+		SplatBin o;
+		{
+			const int* srcw = reinterpret_cast<const int*>( &sb );
+			int* dstw = reinterpret_cast<int*>( &o );
 #pragma unroll
-		for( int o = 1; o < 32; o <<= 1 )
-		{
-			unsigned long long t = __shfl_up_sync( 0xffffffffu, incl, o );
-			if( lane >= o )
-				incl += t;
+			for( int w = 0; w < (int)( sizeof( SplatBin ) / 4 ); w++ )
+				dstw[w] = __shfl_sync( 0xffffffffu, srcw[w], j );
 		}
-		if( lane == 31 )
-			wtot[warp] = incl;
-		__syncthreads();
-		unsigned long long wb = 0, tot = 0;
-		for( int w = 0; w < 32; w++ )
+		const int gj = gi - lane + j;
+		for( int ty = o.ty0 + lane; ty <= o.ty1; ty += 32 )
 		{
-			unsigned long long t = wtot[w];
-			if( w < warp )
-				wb += t;
-			tot += t;
-		}
-		unsigned long long carry = carry_s;
-		if( i < nb )
-			block_base[i] = carry + wb + incl - v;
-		__syncthreads();
-		if( threadIdx.x == 0 )
-			carry_s = carry + tot;
-		__syncthreads();
-	}
-	if( threadIdx.x == 0 )
-	{
-		unsigned long long total = carry_s;
-		st->n_keys = total;
-		st->need_capacity = ( total > capacity ) ? total : 0ull;
-	}
-}
-
-// One warp per 32 splats; for each of them the 32 lanes write its tile keys side by side (coalesced).
-__global__ void __launch_bounds__( 256 ) k_emit( Geometry g, const ushort4* __restrict__ rect,
-                                                 const unsigned* __restrict__ cnt_local,
-                                                 const unsigned long long* __restrict__ block_base,
-                                                 unsigned* __restrict__ keys, unsigned* __restrict__ vals,
-                                                 const DevState* __restrict__ st )
-{
-	if( st->need_capacity )
-		return;
-	const int lane = threadIdx.x & 31;
-	const int gi = ( blockIdx.x * 256 + threadIdx.x );
-	ushort4 rc = make_ushort4( 1, 1, 0, 0 );
-	unsigned long long off = 0;
-	if( gi < g.n_total )
-	{
-		rc = rect[gi];
-		off = block_base[gi / PRE_THREADS] + cnt_local[gi];
-	}
-	const int w = (int)rc.z - (int)rc.x + 1, h = (int)rc.w - (int)rc.y + 1; // empty rect is stored as (1,1,0,0): w = 0
-	const unsigned my_cnt = ( w > 0 && h > 0 ) ? (unsigned)( w * h ) : 0u;
-	const int img_tile_base = ( gi < g.n_total ) ? ( gi / g.n_splats ) * g.tiles_y : 0;
-#pragma unroll 1
-	for( int j = 0; j < 32; j++ )
-	{
-		unsigned c = __shfl_sync( 0xffffffffu, my_cnt, j );
-		if( c == 0 )
-			continue;
-		unsigned long long o = __shfl_sync( 0xffffffffu, off, j );
-		int jw = __shfl_sync( 0xffffffffu, w, j );
-		int jx0 = __shfl_sync( 0xffffffffu, (int)rc.x, j );
-		int jy0 = __shfl_sync( 0xffffffffu, (int)rc.y, j );
-		int jbase = __shfl_sync( 0xffffffffu, img_tile_base, j );
-		int jg = __shfl_sync( 0xffffffffu, gi, j );
-		for( unsigned e = lane; e < c; e += 32 )
-		{
-			int ty = (int)( e / (unsigned)jw ), tx = (int)( e - (unsigned)ty * (unsigned)jw );
-			unsigned tile = (unsigned)( ( jbase + jy0 + ty ) * g.tiles_x + jx0 + tx );
-			keys[o + e] = tile;
-			vals[o + e] = (unsigned)jg;
+			int lo, hi;
+			if( !tile_span( o.k, ty, g.H, o.rtx0, o.rtx1, lo, hi ) )
+				continue;
+			const unsigned n = (unsigned)( hi - lo + 1 );
+			unsigned long long pos = atomicAdd( &st->n_keys, (unsigned long long)n );
+			if( pos + n > capacity )
+				continue;
+			const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
+			for( int tx = lo; tx <= hi; tx++, pos++ )
+			{
+				pair_tile[pos] = row + (unsigned)tx;
+				pair_splat[pos] = (unsigned)gj;
+				atomicAdd( &tile_cnt[row + (unsigned)tx], 1u );
+			}
 		}
 	}
 }
 
-// ------------------------------------------------------------------------------------------------ radix sort ---
-__global__ void __launch_bounds__( RADIX_THREADS ) k_radix_hist( const unsigned* __restrict__ keys, int shift,
-                                                                 unsigned* __restrict__ hist, unsigned max_chunks,
-                                                                 const DevState* __restrict__ st )
-{
-	__shared__ unsigned h[RADIX_BINS];
-	const unsigned long long n = st->need_capacity ? 0ull : st->n_keys;
-	const unsigned long long base = (unsigned long long)blockIdx.x * RADIX_CHUNK;
-	h[threadIdx.x] = 0;
-	__syncthreads();
-	if( base < n )
-	{
-#pragma unroll
-		for( int i = 0; i < RADIX_ITEMS; i++ )
-		{
-			unsigned long long idx = base + (unsigned)( i * RADIX_THREADS ) + threadIdx.x;
-			if( idx < n )
-				atomicAdd( &h[( keys[idx] >> shift ) & ( RADIX_BINS - 1 )], 1u );
-		}
-	}
-	__syncthreads();
-	hist[threadIdx.x * max_chunks + blockIdx.x] = h[threadIdx.x];
-}
-
-// generic in-place exclusive scan of a u32 array (three launches)
+// ------------------------------------------------------------------------------- exclusive scan of the counts ---
 #define SCAN_THREADS 256
 #define SCAN_PER_BLOCK 1024
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( unsigned* __restrict__ a, unsigned n,
+// cursor[i] = block-local exclusive scan of cnt[i]; sums[block] = block total
+__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( const unsigned* __restrict__ cnt,
+                                                                unsigned* __restrict__ cursor, unsigned n,
                                                                 unsigned* __restrict__ sums )
 {
 	__shared__ unsigned wtot[SCAN_THREADS / 32];
@@ -268,7 +291,7 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( unsigned* __rest
 	unsigned v[4];
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
-		v[k] = ( i0 + k < n ) ? a[i0 + k] : 0u;
+		v[k] = ( i0 + k < n ) ? cnt[i0 + k] : 0u;
 	unsigned tsum = v[0] + v[1] + v[2] + v[3], incl = tsum;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -295,19 +318,25 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( unsigned* __rest
 	for( int k = 0; k < 4; k++ )
 	{
 		if( i0 + k < n )
-			a[i0 + k] = run;
+			cursor[i0 + k] = run;
 		run += v[k];
 	}
 	if( threadIdx.x == 0 )
 		sums[blockIdx.x] = tot;
 }
-__global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ sums, unsigned nb )
+// one block: exclusive scan of the block totals; the capacity check of the iteration
+__global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ sums, unsigned nb,
+                                                       unsigned long long capacity, DevState* __restrict__ st )
 {
 	__shared__ unsigned wtot[32];
 	__shared__ unsigned carry_s;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	if( threadIdx.x == 0 )
+	{
 		carry_s = 0;
+		// n_keys was accumulated by k_preprocess (every pair reserved, written or not)
+		st->need_capacity = ( st->n_keys > capacity ) ? st->n_keys : 0ull;
+	}
 	__syncthreads();
 	for( unsigned base = 0; base < nb; base += 1024 )
 	{
@@ -340,7 +369,7 @@ __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ su
 		__syncthreads();
 	}
 }
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ a, unsigned n,
+__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ cursor, unsigned n,
                                                               const unsigned* __restrict__ sums )
 {
 	const unsigned add = sums[blockIdx.x];
@@ -348,87 +377,91 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restri
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
 		if( i0 + k < n )
-			a[i0 + k] += add;
+			cursor[i0 + k] += add;
 }
 
-// Stable scatter of one chunk. Warp w owns keys [base + 512 w, base + 512 (w+1)) and walks them in 16 rounds of 32
-// consecutive keys; match.any gives every key its rank among equal digits of the round, a per-warp digit counter
-// carries the rank across rounds, an exclusive scan over the 8 warps (+ the scanned global histogram) the rest.
-__global__ void __launch_bounds__( RADIX_THREADS ) k_radix_scatter(
-    const unsigned* __restrict__ keys_in, const unsigned* __restrict__ vals_in, unsigned* __restrict__ keys_out,
-    unsigned* __restrict__ vals_out, const unsigned* __restrict__ hist_scanned, unsigned max_chunks, int shift,
-    const DevState* __restrict__ st )
+// ------------------------------------------------------------------------------------------- bucket and sort ---
+__global__ void __launch_bounds__( 256 ) k_bucket( const unsigned* __restrict__ pair_tile,
+                                                   const unsigned* __restrict__ pair_splat,
+                                                   unsigned* __restrict__ cursor, unsigned* __restrict__ list,
+                                                   const DevState* __restrict__ st )
 {
-	__shared__ unsigned wcnt[RADIX_THREADS / 32][RADIX_BINS];
-	const unsigned long long n = st->need_capacity ? 0ull : st->n_keys;
-	const unsigned long long base = (unsigned long long)blockIdx.x * RADIX_CHUNK;
-	if( base >= n )
+	if( st->need_capacity )
 		return;
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-	for( int w = 0; w < RADIX_THREADS / 32; w++ )
-		wcnt[w][threadIdx.x] = 0;
-	__syncthreads();
+	const unsigned long long n = st->n_keys;
+	const unsigned long long stride = (unsigned long long)gridDim.x * 256;
+	for( unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride )
+	{
+		const unsigned slot = atomicAdd( &cursor[pair_tile[i]], 1u );
+		list[slot] = pair_splat[i];
+	}
+}
 
-	const unsigned long long seg = base + (unsigned)( warp * ( RADIX_CHUNK / ( RADIX_THREADS / 32 ) ) );
-	unsigned key[RADIX_ITEMS];
-	unsigned short pos[RADIX_ITEMS];
-	const unsigned lt = ( 1u << lane ) - 1u;
-#pragma unroll
-	for( int r = 0; r < RADIX_ITEMS; r++ )
+// compare-exchange network step of the normalised bitonic sort: every comparison is ascending, so entries beyond n
+// behave as +inf padding without being stored
+template <typename Ptr>
+__device__ __forceinline__ void bitonic_sort( Ptr a, unsigned n, int tid )
+{
+	unsigned P = 2;
+	while( P < n )
+		P <<= 1;
+	for( unsigned k = 2; k <= P; k <<= 1 )
 	{
-		unsigned long long idx = seg + (unsigned)( r * 32 ) + lane;
-		bool valid = idx < n;
-		unsigned k = valid ? keys_in[idx] : 0xffffffffu;
-		unsigned dg = valid ? ( ( k >> shift ) & ( RADIX_BINS - 1 ) ) : RADIX_BINS;
-		unsigned peers = __match_any_sync( 0xffffffffu, dg );
-		unsigned pre = valid ? wcnt[warp][dg] : 0u;
-		__syncwarp();
-		if( valid && ( peers & lt ) == 0u )
-			wcnt[warp][dg] = pre + __popc( peers );
-		__syncwarp();
-		key[r] = k;
-		pos[r] = (unsigned short)( pre + __popc( peers & lt ) );
-	}
-	__syncthreads();
-	{
-		unsigned run = hist_scanned[threadIdx.x * max_chunks + blockIdx.x];
-#pragma unroll
-		for( int w = 0; w < RADIX_THREADS / 32; w++ )
+		for( unsigned j = k >> 1; j > 0; j >>= 1 )
 		{
-			unsigned c = wcnt[w][threadIdx.x];
-			wcnt[w][threadIdx.x] = run;
-			run += c;
-		}
-	}
-	__syncthreads();
-#pragma unroll
-	for( int r = 0; r < RADIX_ITEMS; r++ )
-	{
-		unsigned long long idx = seg + (unsigned)( r * 32 ) + lane;
-		if( idx < n )
-		{
-			unsigned dg = ( key[r] >> shift ) & ( RADIX_BINS - 1 );
-			unsigned dst = wcnt[warp][dg] + pos[r];
-			keys_out[dst] = key[r];
-			vals_out[dst] = vals_in[idx];
+			const bool first = ( j == ( k >> 1 ) );
+			for( unsigned t = tid; t < ( P >> 1 ); t += SORT_THREADS )
+			{
+				// t-th comparator of this step: i has bit j clear
+				const unsigned i = ( ( t & ~( j - 1u ) ) << 1 ) | ( t & ( j - 1u ) );
+				const unsigned l = first ? ( i ^ ( k - 1u ) ) : ( i | j );
+				if( l < n )
+				{
+					const unsigned x = a[i], y = a[l];
+					if( x > y )
+					{
+						a[i] = y;
+						a[l] = x;
+					}
+				}
+			}
+			__syncthreads();
 		}
 	}
 }
 
-__global__ void __launch_bounds__( 256 ) k_tile_ranges( const unsigned* __restrict__ keys,
-                                                        uint2* __restrict__ tile_range,
-                                                        const DevState* __restrict__ st )
+__global__ void __launch_bounds__( SORT_THREADS ) k_tile_sort( Geometry g, const unsigned* __restrict__ tile_cnt,
+                                                               const unsigned* __restrict__ cursor,
+                                                               unsigned* __restrict__ list,
+                                                               uint2* __restrict__ tile_range,
+                                                               const DevState* __restrict__ st )
 {
-	const unsigned long long n = st->need_capacity ? 0ull : st->n_keys;
-	const unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x;
-	if( i >= n )
+	__shared__ unsigned sm[SORT_SMEM_MAX];
+	const unsigned tile = blockIdx.x;
+	if( st->need_capacity )
 		return;
-	const unsigned k = keys[i];
-	if( i == 0 || keys[i - 1] != k )
-		tile_range[k].x = (unsigned)i;
-	if( i + 1 == n || keys[i + 1] != k )
-		tile_range[k].y = (unsigned)( i + 1 );
+	const unsigned n = tile_cnt[tile];
+	const unsigned end = cursor[tile]; // every entry of the bucket has been placed: the cursor sits at its end
+	const unsigned start = end - n;
+	if( threadIdx.x == 0 )
+		tile_range[tile] = make_uint2( start, end );
+	if( n < 2 )
+		return;
+	unsigned* p = list + start;
+	if( n <= SORT_SMEM_MAX )
+	{
+		for( unsigned i = threadIdx.x; i < n; i += SORT_THREADS )
+			sm[i] = p[i];
+		__syncthreads();
+		bitonic_sort( sm, n, threadIdx.x );
+		for( unsigned i = threadIdx.x; i < n; i += SORT_THREADS )
+			p[i] = sm[i];
+	}
+	else
+	{
+		__syncthreads();
+		bitonic_sort( p, n, threadIdx.x ); // in place in HBM/L2; __syncthreads orders the CTA's global accesses
+	}
 }
 
 // ---------------------------------------------------------------------------------------------------- launch ---
@@ -436,50 +469,29 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
                                cudaEvent_t after_emit )
 {
 	int launches = 0;
+	*sorted_buf = 1; // the sorted lists live in vals[1]; keys[0] / vals[0] hold the unordered pairs
+	cudaMemsetAsync( &b.state->n_keys, 0, 2 * sizeof( unsigned long long ), s );
 	if( g.n_total == 0 )
 	{
 		cudaMemsetAsync( b.tile_range, 0, sizeof( uint2 ) * (size_t)g.n_tiles_total, s );
-		cudaMemsetAsync( &b.state->n_keys, 0, 2 * sizeof( unsigned long long ), s );
-		*sorted_buf = 0;
 		if( after_emit )
 			cudaEventRecord( after_emit, s );
 		return 0;
 	}
+	const unsigned nt = (unsigned)g.n_tiles_total;
+	cudaMemsetAsync( b.tile_cnt, 0, sizeof( unsigned ) * (size_t)nt, s );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
-	unsigned* block_sum = reinterpret_cast<unsigned*>( b.scan_tmp );         // [nb] u32
-	unsigned long long* block_base = b.scan_tmp + ( ( nb + 1 ) / 2 + 1 );      // [nb] u64
-	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rect, b.cnt, block_sum );
-	k_scan_top<<<1, 1024, 0, s>>>( block_sum, nb, block_base, b.capacity, b.state );
-	k_emit<<<nb, 256, 0, s>>>( g, b.rect, b.cnt, block_base, b.keys[0], b.vals[0], b.state );
-	launches += 3;
+	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.tile_cnt, b.keys[0], b.vals[0], b.capacity,
+	                                         gs2d_tune( "GS2D_CULL", 1 ), b.state );
+	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
-
-	int bits = 0;
-	while( ( 1ll << bits ) < (long long)g.n_tiles_total )
-		bits++;
-	const int passes = ( bits + RADIX_BITS - 1 ) / RADIX_BITS;
-	const unsigned chunks = b.max_chunks;
-	const unsigned hist_n = RADIX_BINS * chunks;
-	const unsigned scan_nb = ( hist_n + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
-	unsigned* scan_sums = b.radix_hist + hist_n;
-	int cur = 0;
-	for( int p = 0; p < passes; p++ )
-	{
-		const int shift = p * RADIX_BITS;
-		k_radix_hist<<<chunks, RADIX_THREADS, 0, s>>>( b.keys[cur], shift, b.radix_hist, chunks, b.state );
-		k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( b.radix_hist, hist_n, scan_sums );
-		k_scan_sums<<<1, 1024, 0, s>>>( scan_sums, scan_nb );
-		k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.radix_hist, hist_n, scan_sums );
-		k_radix_scatter<<<chunks, RADIX_THREADS, 0, s>>>( b.keys[cur], b.vals[cur], b.keys[cur ^ 1], b.vals[cur ^ 1],
-		                                                  b.radix_hist, chunks, shift, b.state );
-		launches += 5;
-		cur ^= 1;
-	}
-	cudaMemsetAsync( b.tile_range, 0, sizeof( uint2 ) * (size_t)g.n_tiles_total, s );
-	const unsigned long long cap_blocks = ( b.capacity + 255 ) / 256;
-	k_tile_ranges<<<(unsigned)cap_blocks, 256, 0, s>>>( b.keys[cur], b.tile_range, b.state );
-	launches += 1;
-	*sorted_buf = cur;
+	const unsigned scan_nb = ( nt + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( b.tile_cnt, b.tile_cur, nt, b.scan_sums );
+	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
+	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.tile_cur, nt, b.scan_sums );
+	k_bucket<<<148 * 16, 256, 0, s>>>( b.keys[0], b.vals[0], b.tile_cur, b.vals[1], b.state );
+	k_tile_sort<<<nt, SORT_THREADS, 0, s>>>( g, b.tile_cnt, b.tile_cur, b.vals[1], b.tile_range, b.state );
+	launches += 5;
 	return launches;
 }

@@ -156,16 +156,13 @@ struct Buffers
 	float* adam_m;  // [9][n_pad]
 	float* adam_v;  // [9][n_pad]
 	SplatRec* rec;  // [n_total]
-	ushort4* rect;  // [n_total]
-	unsigned* cnt;  // [n_total]
-	unsigned long long* offs; // [n_total] exclusive scan of cnt
-	unsigned long long* scan_tmp;
-	unsigned* keys[2];
-	unsigned* vals[2];
+	unsigned* tile_cnt;   // [n_tiles_total] list entries per tile
+	unsigned* tile_cur;   // [n_tiles_total] bucket cursor: exclusive scan of tile_cnt, advanced to the bucket end
+	unsigned* scan_sums;  // scratch of the scan
+	unsigned* keys[2];    // keys[0]: tile id of the unordered (tile, splat) pairs; keys[1] unused
+	unsigned* vals[2];    // vals[0]: splat index of the pairs; vals[1]: the per-tile lists, ordered by splat index
 	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward)
 	unsigned long long capacity;
-	unsigned* radix_hist;     // [256][max_chunks]
-	unsigned max_chunks;
 	uint2* tile_range;        // [n_tiles_total]
 	float4* target;           // [n_images][H][W]
 	float4* image;            // [n_images][H][W]

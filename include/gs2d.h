@@ -156,6 +156,10 @@ int gs2d_profile_step( gs2d_ctx* ctx, float out_ms[6] );
  * (same order as gs2d_profile_step) and the number of iterations measured. gs2d_set_profiling resets the sums. */
 int gs2d_set_profiling( gs2d_ctx* ctx, int enable );
 int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
+/* Developer knobs (process-wide; same names as the environment variables they override): "GS2D_CULL" 0/1 = bin
+ * with the conservative tile rectangle only / with the per-tile-row ellipse spans (default; same images, fewer keys),
+ * "GS2D_FWD_MINB" 32/24/20 and "GS2D_BWD_MINB" 20/16 = register caps of the blend kernels. */
+int gs2d_set_tuning( const char* name, int value );
 /* Work counters on/off (default on): while off, the forward blend launched by gs2d_step does not count live pairs
  * (one instruction per 8x4 block visit); gs2d_forward / gs2d_backward always count. */
 int gs2d_set_stats( gs2d_ctx* ctx, int enable );

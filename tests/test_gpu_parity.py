@@ -202,6 +202,32 @@ def test_edge_cases():
     assert_grads_close(g[ok], g_cpu[ok], rtol=1e-3)
 
 
+def test_ellipse_culling_is_a_superset_of_the_footprint():
+    """Binning with the per-tile-row ellipse spans must render bit-identical images to binning with the conservative
+    rectangle (any dropped (tile, splat) pair that covers a pixel changes that pixel), with fewer list entries."""
+    W, H, n = 700, 520, 6000
+    rng = np.random.default_rng(11)
+    cases = [random_splats(rng, W, H, n, smin=2, smax=14), random_splats(rng, W, H, 400, smin=20, smax=160),
+             random_splats(rng, W, H, 3000, smin=1, smax=40)]
+    cases[2]["sy"][:] = np.random.default_rng(5).uniform(1, 2.5, 3000)  # needles at every angle
+    for splats in cases:
+        out = []
+        for cull in (0, 1):
+            gs2d.set_tuning("GS2D_CULL", cull)
+            try:
+                with gs2d.Fitter(W, H, len(splats)) as fit:
+                    fit.set_target(gs2d.synth_target(W, H, seed=3))
+                    fit.upload(splats)
+                    fit.forward()
+                    out.append((fit.image(), fit.stats()))
+            finally:
+                gs2d.set_tuning("GS2D_CULL", 1)
+        (img0, st0), (img1, st1) = out
+        assert img0.tobytes() == img1.tobytes()
+        assert st0["live_pairs"] == st1["live_pairs"]
+        assert st1["keys"] < st0["keys"]
+
+
 def test_nonfinite_is_reported_not_aborted():
     W, H = 64, 64
     s = ob.init_splats(W, H, 8)
