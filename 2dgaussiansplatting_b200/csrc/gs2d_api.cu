@@ -223,6 +223,10 @@ static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
 	CK( cudaMalloc( &b.vals[0], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.vals[1], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * 8 * capacity ) );
+	if( b.pair_rank )
+		cudaFree( b.pair_rank );
+	b.pair_rank = nullptr;
+	CK( cudaMalloc( &b.pair_rank, sizeof( unsigned short ) * capacity ) );
 	b.capacity = capacity;
 	return GS2D_OK;
 }
@@ -246,7 +250,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->comm && g_nccl.CommDestroy )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
-	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.tile_cnt, b.tile_cur,
+	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.pair_rank,
 	                 b.scan_sums,  b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage };
@@ -324,6 +328,19 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	g.tiles_x = ( W + GS2D_TILE - 1 ) / GS2D_TILE;
 	g.tiles_y = ( H + GS2D_TILE - 1 ) / GS2D_TILE;
 	g.n_tiles_total = n_images * g.tiles_x * g.tiles_y;
+	g.nt_pad = ( g.n_tiles_total + 3 ) & ~3;
+	// index slices: buckets of ~3 entries at the reference density (~14 tiles per splat), 16-bit bucket counters
+	g.n_slices = 1;
+	while( g.n_slices < 64 && (long long)g.n_slices * 4 * g.tiles_x * g.tiles_y < (long long)n_splats * 14 )
+		g.n_slices *= 2;
+	while( ( n_splats + g.n_slices - 1 ) / g.n_slices > 65535 )
+		g.n_slices *= 2;
+	g.slice_size = std::max( 1, ( n_splats + g.n_slices - 1 ) / g.n_slices );
+	if( (long long)g.n_tiles_total * g.n_slices > 0x7FFF0000ll )
+	{
+		delete c;
+		return GS2D_ERR_INVALID;
+	}
 	g.min_throughput = c->hp.min_throughput;
 	set_band( c, 0, 1 );
 
@@ -336,9 +353,10 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.adam_m, plane_bytes ) );
 	CKC( cudaMalloc( &b.adam_v, plane_bytes ) );
 	CKC( cudaMalloc( &b.rec, sizeof( SplatRec ) * (size_t)std::max( g.n_total, 1 ) ) );
-	CKC( cudaMalloc( &b.tile_cnt, sizeof( unsigned ) * ( (size_t)g.n_tiles_total + 4 ) ) );
-	CKC( cudaMalloc( &b.tile_cur, sizeof( unsigned ) * ( (size_t)g.n_tiles_total + 4 ) ) );
-	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( (size_t)g.n_tiles_total / 1024 + 16 ) ) );
+	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
+	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices ) );
+	CKC( cudaMalloc( &b.bucket_off, sizeof( unsigned ) * ( n_buckets + 4 ) ) );
+	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( n_buckets / 1024 + 16 ) ) );
 	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );

@@ -4,24 +4,24 @@
 // and scan-converting each one (main.cpp:419-538): here every 16x16 tile gets the list of splats whose footprint
 // may touch it, ordered by splat index (== the reference's blend order).
 //
-// The (tile | order) keys are sorted MSD-first, and the first digit is the whole tile id:
+// The (tile | order) keys are sorted MSD-first without a sorting pass over the keys:
+//   bucket = (tile, index slice): the splat indices of an image are cut into n_slices equal slices (<= 65535 splats
+//   each), so a bucket holds the few splats of one slice that touch one tile (3.3 on average at 4096^2 / 1 M).
 //   k_preprocess   : covariance, inverse, row range (cov_of main.cpp:206-221, :432-436, :489-491) -> 64-byte record;
 //                    the tiles the 3-sigma ellipse can touch (per tile row: the x-extent of the ellipse inside the
-//                    band of that row's pixel centres, see tile_span) are counted per tile (red.add) and written as
-//                    unordered (tile, splat) pairs
-//   k_scan_*       : exclusive scan of the tile counts = bucket offsets; total key count and the capacity check
-//   k_bucket       : one thread per pair: slot = atomicAdd( cursor[tile], 1 ) -> the splat index lands in its tile's
-//                    bucket (arbitrary order inside the bucket)
-//   k_tile_sort    : one CTA per tile sorts its bucket by splat index in shared memory (normalised bitonic network,
-//                    virtual +inf padding; buckets beyond the shared-memory size are sorted in place in HBM) and
-//                    writes the tile's [start,end)
-// Splat indices are unique inside a bucket, so the sorted lists — and everything downstream — are deterministic
-// although the bucket pass uses atomics.
+//                    band of that row's pixel centres, see tile_span) are emitted as unordered (bucket, splat, rank)
+//                    triples, rank = arrival order in the bucket. The bucket counters are 16 bits wide and the
+//                    counters of 4 consecutive tiles share one 64-bit word, so ONE atomicAdd serves up to 4 tiles
+//                    of a tile row (the L2 atomic rate, not HBM, bounds this kernel).
+//   k_scan_*       : exclusive scan of the bucket counts in (tile, slice) order = bucket offsets; capacity check
+//   k_place        : one thread per triple: list[offset[bucket] + rank] = splat (no atomics)
+//   k_rank         : one thread per bucket orders its few entries by splat index (rank by counting) and the first /
+//                    last bucket of a tile write the tile's [start,end)
+// Splat indices are unique inside a bucket, so the sorted lists - and everything downstream - are deterministic
+// although the arrival order inside a bucket is not.
 #include "gs2d_internal.cuh"
 
 #define PRE_THREADS 256
-#define SORT_THREADS 128
-#define SORT_SMEM_MAX 4096   // bucket entries sorted in shared memory (16 KB); longer buckets are sorted in HBM
 
 // Conservative column span [tx_lo, tx_hi] of the tiles of tile row ty that the splat's footprint can touch.
 // The reference covers pixel (x, y) iff begY <= y <= endY and x in [(int)(px+u0), (int)(px+u1)], u0/u1 the chord of the
@@ -66,6 +66,7 @@ __device__ __forceinline__ bool tile_span( const SpanConsts& k, int ty, int H, i
 	return tx_lo <= tx_hi;
 }
 
+
 // ------------------------------------------------------------------------------------------------ preprocess ---
 // Per-splat part: record + span constants + conservative tile rectangle (tile units; empty if rtx0 > rtx1).
 struct SplatBin
@@ -73,15 +74,41 @@ struct SplatBin
 	SpanConsts k;
 	int rtx0, rtx1, ty0, ty1;
 	int tile_base; // first tile id of the splat's image
+	int slice;     // index slice of the splat
 };
 
 #define BIG_RECT 1024 // rectangles with more tiles than this are binned by the whole warp
 
+struct PairOut
+{
+	unsigned* bucket;            // tile * n_slices + slice
+	unsigned* splat;
+	unsigned short* rank;        // arrival order inside the bucket
+	unsigned long long* cnt64;   // [n_slices][nt_pad / 4] words of four 16-bit bucket counters (consecutive tiles)
+};
+
+// Emit the pairs of tiles id_lo..id_hi (one tile row of one splat) at pos.., one 64-bit atomic per 4-tile group.
+__device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
+                                          int slice, unsigned splat, unsigned long long pos )
+{
+	unsigned long long* cnt = o.cnt64 + (size_t)slice * ( g.nt_pad >> 2 );
+	for( unsigned grp = id_lo >> 2; grp <= ( id_hi >> 2 ); grp++ )
+	{
+		const unsigned f0 = max( id_lo, grp * 4u ) - grp * 4u, f1 = min( id_hi, grp * 4u + 3u ) - grp * 4u;
+		// ones in the 16-bit fields f0..f1
+		const unsigned long long add = ( 0x0001000100010001ull >> ( 16u * ( 3u - ( f1 - f0 ) ) ) ) << ( 16u * f0 );
+		const unsigned long long old = atomicAdd( cnt + grp, add );
+		for( unsigned f = f0; f <= f1; f++, pos++ )
+		{
+			o.bucket[pos] = ( grp * 4u + f ) * (unsigned)g.n_slices + (unsigned)slice;
+			o.splat[pos] = splat;
+			o.rank[pos] = (unsigned short)( old >> ( 16u * f ) );
+		}
+	}
+}
+
 __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const float* __restrict__ params,
-                                                               SplatRec* __restrict__ rec,
-                                                               unsigned* __restrict__ tile_cnt,
-                                                               unsigned* __restrict__ pair_tile,
-                                                               unsigned* __restrict__ pair_splat,
+                                                               SplatRec* __restrict__ rec, PairOut out,
                                                                unsigned long long capacity, int cull,
                                                                DevState* __restrict__ st )
 {
@@ -93,6 +120,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 	sb.ty0 = 1;
 	sb.ty1 = 0;
 	sb.tile_base = 0;
+	sb.slice = 0;
 	sb.k.begY = 1;
 	sb.k.endY = 0;
 	if( gi < g.n_total )
@@ -170,7 +198,9 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			sb.rtx0 = x0 / GS2D_TILE;
 			sb.rtx1 = x1 / GS2D_TILE;
 		}
-		sb.tile_base = ( gi / g.n_splats ) * g.tiles_y * g.tiles_x;
+		const int img = gi / g.n_splats;
+		sb.tile_base = img * g.tiles_y * g.tiles_x;
+		sb.slice = ( gi - img * g.n_splats ) / g.slice_size;
 		sb.k.px = px;
 		sb.k.py = py;
 		sb.k.a = a;
@@ -223,7 +253,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		block_base = total ? atomicAdd( &st->n_keys, (unsigned long long)total ) : 0ull;
 	__syncthreads();
 
-	// phase B: write the pairs and count them per tile
+	// phase B: emit the pairs
 	if( cnt && block_base + total <= capacity )
 	{
 		unsigned long long pos = block_base + wbase + incl - cnt;
@@ -233,12 +263,8 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			if( !tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
 				continue;
 			const unsigned row = (unsigned)( sb.tile_base + ty * g.tiles_x );
-			for( int tx = lo; tx <= hi; tx++, pos++ )
-			{
-				pair_tile[pos] = row + (unsigned)tx;
-				pair_splat[pos] = (unsigned)gi;
-				atomicAdd( &tile_cnt[row + (unsigned)tx], 1u );
-			}
+			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, sb.slice, (unsigned)gi, pos );
+			pos += (unsigned)( hi - lo + 1 );
 		}
 	}
 
@@ -264,16 +290,11 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			if( !tile_span( o.k, ty, g.H, o.rtx0, o.rtx1, lo, hi ) )
 				continue;
 			const unsigned n = (unsigned)( hi - lo + 1 );
-			unsigned long long pos = atomicAdd( &st->n_keys, (unsigned long long)n );
+			const unsigned long long pos = atomicAdd( &st->n_keys, (unsigned long long)n );
 			if( pos + n > capacity )
 				continue;
 			const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-			for( int tx = lo; tx <= hi; tx++, pos++ )
-			{
-				pair_tile[pos] = row + (unsigned)tx;
-				pair_splat[pos] = (unsigned)gj;
-				atomicAdd( &tile_cnt[row + (unsigned)tx], 1u );
-			}
+			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, o.slice, (unsigned)gj, pos );
 		}
 	}
 }
@@ -281,9 +302,17 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 // ------------------------------------------------------------------------------- exclusive scan of the counts ---
 #define SCAN_THREADS 256
 #define SCAN_PER_BLOCK 1024
-// cursor[i] = block-local exclusive scan of cnt[i]; sums[block] = block total
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( const unsigned* __restrict__ cnt,
-                                                                unsigned* __restrict__ cursor, unsigned n,
+// scan index i = tile * n_slices + slice; the 16-bit counter of bucket i lives at cnt16[slice * nt_pad + tile]
+__device__ __forceinline__ unsigned bucket_count( const Geometry& g, const unsigned short* __restrict__ cnt16,
+                                                  unsigned i )
+{
+	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
+	return cnt16[(size_t)slice * g.nt_pad + tile];
+}
+
+// offset[i] = block-local exclusive scan of the bucket counts; sums[block] = block total
+__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( Geometry g, const unsigned short* __restrict__ cnt16,
+                                                                unsigned* __restrict__ offset, unsigned n,
                                                                 unsigned* __restrict__ sums )
 {
 	__shared__ unsigned wtot[SCAN_THREADS / 32];
@@ -291,7 +320,7 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( const unsigned* 
 	unsigned v[4];
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
-		v[k] = ( i0 + k < n ) ? cnt[i0 + k] : 0u;
+		v[k] = ( i0 + k < n ) ? bucket_count( g, cnt16, i0 + k ) : 0u;
 	unsigned tsum = v[0] + v[1] + v[2] + v[3], incl = tsum;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -318,7 +347,7 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( const unsigned* 
 	for( int k = 0; k < 4; k++ )
 	{
 		if( i0 + k < n )
-			cursor[i0 + k] = run;
+			offset[i0 + k] = run;
 		run += v[k];
 	}
 	if( threadIdx.x == 0 )
@@ -369,7 +398,7 @@ __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ su
 		__syncthreads();
 	}
 }
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ cursor, unsigned n,
+__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ offset, unsigned n,
                                                               const unsigned* __restrict__ sums )
 {
 	const unsigned add = sums[blockIdx.x];
@@ -377,91 +406,59 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restri
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
 		if( i0 + k < n )
-			cursor[i0 + k] += add;
+			offset[i0 + k] += add;
 }
 
-// ------------------------------------------------------------------------------------------- bucket and sort ---
-__global__ void __launch_bounds__( 256 ) k_bucket( const unsigned* __restrict__ pair_tile,
-                                                   const unsigned* __restrict__ pair_splat,
-                                                   unsigned* __restrict__ cursor, unsigned* __restrict__ list,
-                                                   const DevState* __restrict__ st )
+// ------------------------------------------------------------------------------------------- place and order ---
+__global__ void __launch_bounds__( 256 ) k_place( PairOut in, const unsigned* __restrict__ offset,
+                                                  unsigned* __restrict__ list, const DevState* __restrict__ st )
 {
 	if( st->need_capacity )
 		return;
 	const unsigned long long n = st->n_keys;
 	const unsigned long long stride = (unsigned long long)gridDim.x * 256;
 	for( unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride )
-	{
-		const unsigned slot = atomicAdd( &cursor[pair_tile[i]], 1u );
-		list[slot] = pair_splat[i];
-	}
+		list[offset[in.bucket[i]] + in.rank[i]] = in.splat[i];
 }
 
-// compare-exchange network step of the normalised bitonic sort: every comparison is ascending, so entries beyond n
-// behave as +inf padding without being stored
-template <typename Ptr>
-__device__ __forceinline__ void bitonic_sort( Ptr a, unsigned n, int tid )
+// One thread per bucket: order its entries by splat index (rank by counting: the indices are unique), list -> out.
+__global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned short* __restrict__ cnt16,
+                                                 const unsigned* __restrict__ offset,
+                                                 const unsigned* __restrict__ list, unsigned* __restrict__ out,
+                                                 uint2* __restrict__ tile_range, unsigned n_buckets,
+                                                 const DevState* __restrict__ st )
 {
-	unsigned P = 2;
-	while( P < n )
-		P <<= 1;
-	for( unsigned k = 2; k <= P; k <<= 1 )
-	{
-		for( unsigned j = k >> 1; j > 0; j >>= 1 )
-		{
-			const bool first = ( j == ( k >> 1 ) );
-			for( unsigned t = tid; t < ( P >> 1 ); t += SORT_THREADS )
-			{
-				// t-th comparator of this step: i has bit j clear
-				const unsigned i = ( ( t & ~( j - 1u ) ) << 1 ) | ( t & ( j - 1u ) );
-				const unsigned l = first ? ( i ^ ( k - 1u ) ) : ( i | j );
-				if( l < n )
-				{
-					const unsigned x = a[i], y = a[l];
-					if( x > y )
-					{
-						a[i] = y;
-						a[l] = x;
-					}
-				}
-			}
-			__syncthreads();
-		}
-	}
-}
-
-__global__ void __launch_bounds__( SORT_THREADS ) k_tile_sort( Geometry g, const unsigned* __restrict__ tile_cnt,
-                                                               const unsigned* __restrict__ cursor,
-                                                               unsigned* __restrict__ list,
-                                                               uint2* __restrict__ tile_range,
-                                                               const DevState* __restrict__ st )
-{
-	__shared__ unsigned sm[SORT_SMEM_MAX];
-	const unsigned tile = blockIdx.x;
 	if( st->need_capacity )
 		return;
-	const unsigned n = tile_cnt[tile];
-	const unsigned end = cursor[tile]; // every entry of the bucket has been placed: the cursor sits at its end
-	const unsigned start = end - n;
-	if( threadIdx.x == 0 )
-		tile_range[tile] = make_uint2( start, end );
-	if( n < 2 )
+	const unsigned i = blockIdx.x * 256 + threadIdx.x;
+	if( i >= n_buckets )
 		return;
-	unsigned* p = list + start;
-	if( n <= SORT_SMEM_MAX )
+	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
+	const unsigned n = cnt16[(size_t)slice * g.nt_pad + tile];
+	const unsigned start = offset[i];
+	if( slice == 0 )
+		tile_range[tile].x = start;
+	if( slice == (unsigned)g.n_slices - 1 )
+		tile_range[tile].y = start + n;
+	const unsigned* p = list + start;
+	unsigned* q = out + start;
+	if( n == 1 )
+		q[0] = p[0];
+	else if( n == 2 )
 	{
-		for( unsigned i = threadIdx.x; i < n; i += SORT_THREADS )
-			sm[i] = p[i];
-		__syncthreads();
-		bitonic_sort( sm, n, threadIdx.x );
-		for( unsigned i = threadIdx.x; i < n; i += SORT_THREADS )
-			p[i] = sm[i];
+		const unsigned x = p[0], y = p[1];
+		q[0] = min( x, y );
+		q[1] = max( x, y );
 	}
 	else
-	{
-		__syncthreads();
-		bitonic_sort( p, n, threadIdx.x ); // in place in HBM/L2; __syncthreads orders the CTA's global accesses
-	}
+		for( unsigned a = 0; a < n; a++ )
+		{
+			const unsigned e = p[a];
+			unsigned r = 0;
+			for( unsigned b = 0; b < n; b++ )
+				r += p[b] < e ? 1u : 0u;
+			q[r] = e;
+		}
 }
 
 // ---------------------------------------------------------------------------------------------------- launch ---
@@ -469,7 +466,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
                                cudaEvent_t after_emit )
 {
 	int launches = 0;
-	*sorted_buf = 1; // the sorted lists live in vals[1]; keys[0] / vals[0] hold the unordered pairs
+	*sorted_buf = 0; // the ordered lists end up in vals[0] (the splat column of the triples is dead by then)
 	cudaMemsetAsync( &b.state->n_keys, 0, 2 * sizeof( unsigned long long ), s );
 	if( g.n_total == 0 )
 	{
@@ -478,20 +475,25 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 			cudaEventRecord( after_emit, s );
 		return 0;
 	}
-	const unsigned nt = (unsigned)g.n_tiles_total;
-	cudaMemsetAsync( b.tile_cnt, 0, sizeof( unsigned ) * (size_t)nt, s );
+	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
+	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices, s );
+	PairOut po;
+	po.bucket = b.keys[0];
+	po.splat = b.vals[0];
+	po.rank = b.pair_rank;
+	po.cnt64 = reinterpret_cast<unsigned long long*>( b.bucket_cnt );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
-	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.tile_cnt, b.keys[0], b.vals[0], b.capacity,
-	                                         gs2d_tune( "GS2D_CULL", 1 ), b.state );
+	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
-	const unsigned scan_nb = ( nt + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
-	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( b.tile_cnt, b.tile_cur, nt, b.scan_sums );
+	const unsigned scan_nb = ( nbk + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, nbk, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
-	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.tile_cur, nt, b.scan_sums );
-	k_bucket<<<148 * 16, 256, 0, s>>>( b.keys[0], b.vals[0], b.tile_cur, b.vals[1], b.state );
-	k_tile_sort<<<nt, SORT_THREADS, 0, s>>>( g, b.tile_cnt, b.tile_cur, b.vals[1], b.tile_range, b.state );
+	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.bucket_off, nbk, b.scan_sums );
+	k_place<<<148 * 16, 256, 0, s>>>( po, b.bucket_off, b.vals[1], b.state );
+	k_rank<<<( nbk + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.vals[1], b.vals[0], b.tile_range, nbk,
+	                                           b.state );
 	launches += 5;
 	return launches;
 }

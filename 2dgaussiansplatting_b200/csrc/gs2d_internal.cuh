@@ -71,6 +71,8 @@ struct Geometry
 	int tiles_x, tiles_y;    // per image
 	int band_ty0, band_ty1;  // this rank's tile rows [ty0, ty1)
 	int n_tiles_total;       // n_images * tiles_y * tiles_x  (key space)
+	int nt_pad;              // n_tiles_total rounded up to a multiple of 4
+	int n_slices, slice_size; // index slices of an image's splats: slice = i / slice_size, slice_size <= 65535
 	float min_throughput;    // MIN_THROUGHPUT, main.cpp:8
 };
 
@@ -156,11 +158,12 @@ struct Buffers
 	float* adam_m;  // [9][n_pad]
 	float* adam_v;  // [9][n_pad]
 	SplatRec* rec;  // [n_total]
-	unsigned* tile_cnt;   // [n_tiles_total] list entries per tile
-	unsigned* tile_cur;   // [n_tiles_total] bucket cursor: exclusive scan of tile_cnt, advanced to the bucket end
-	unsigned* scan_sums;  // scratch of the scan
-	unsigned* keys[2];    // keys[0]: tile id of the unordered (tile, splat) pairs; keys[1] unused
-	unsigned* vals[2];    // vals[0]: splat index of the pairs; vals[1]: the per-tile lists, ordered by splat index
+	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
+	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
+	unsigned* scan_sums;        // scratch of the scan
+	unsigned* keys[2];          // keys[0]: bucket of the unordered (bucket, splat, rank) triples; keys[1] unused
+	unsigned* vals[2];          // vals[0]: splat of the triples, later the ordered lists; vals[1]: bucketed, unordered
+	unsigned short* pair_rank;  // arrival order of the triple inside its bucket
 	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward)
 	unsigned long long capacity;
 	uint2* tile_range;        // [n_tiles_total]
