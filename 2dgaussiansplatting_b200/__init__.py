@@ -47,6 +47,9 @@ ABI_SYMBOLS = [
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
     "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
+    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
+    "gs2d_image_load_rgba8", "gs2d_image_decode_jpeg_rgba8", "gs2d_image_free", "gs2d_image_write_ppm",
+    "gs2d_overlay_geometry",
 ]
 
 
@@ -119,6 +122,17 @@ def load_library():
     L.gs2d_sync.argtypes = [vp]
     L.gs2d_microbench_fp32.argtypes = [i, C.POINTER(C.c_double)]
     L.gs2d_microbench_hbm.argtypes = [i, C.POINTER(C.c_double)]
+    L.gs2d_get_optimize_opacity.argtypes = [vp, C.POINTER(i)]
+    L.gs2d_get_dims.argtypes = [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)]
+    L.gs2d_save_checkpoint.argtypes = [vp, C.c_char_p]
+    L.gs2d_load_checkpoint.argtypes = [vp, C.c_char_p]
+    u8pp = C.POINTER(C.POINTER(C.c_uint8))
+    L.gs2d_image_load_rgba8.argtypes = [C.c_char_p, u8pp, C.POINTER(i), C.POINTER(i)]
+    L.gs2d_image_decode_jpeg_rgba8.argtypes = [vp, C.c_size_t, u8pp, C.POINTER(i), C.POINTER(i)]
+    L.gs2d_image_free.argtypes = [C.POINTER(C.c_uint8)]
+    L.gs2d_image_free.restype = None
+    L.gs2d_image_write_ppm.argtypes = [C.c_char_p, vp, i, i]
+    L.gs2d_overlay_geometry.argtypes = [vp, i, i, vp, vp]
     _lib = L
     return L
 
@@ -332,6 +346,14 @@ class Fitter:
         self._ck(self.lib.gs2d_launch_count(self._ctx, C.byref(n)))
         return n.value
 
+    # -- checkpoint ----------------------------------------------------------------------------
+    def save_checkpoint(self, path):
+        """{splats, splatAdams, beta1t, beta2t, iterations} of every image (main.cpp:271-278) -> file."""
+        self._ck(self.lib.gs2d_save_checkpoint(self._ctx, os.fsencode(path)))
+
+    def load_checkpoint(self, path):
+        self._ck(self.lib.gs2d_load_checkpoint(self._ctx, os.fsencode(path)))
+
     # -- multi-GPU -----------------------------------------------------------------------------------------------
     def set_band(self, rank, n_ranks):
         self._ck(self.lib.gs2d_set_band(self._ctx, rank, n_ranks))
@@ -339,6 +361,56 @@ class Fitter:
     def comm_init(self, rank, n_ranks, unique_id):
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
         self._ck(self.lib.gs2d_comm_init(self._ctx, rank, n_ranks, buf))
+
+
+def _take_image(rc, p, w, h):
+    L = load_library()
+    if rc != GS2D_OK:
+        raise Gs2dError(rc, L.gs2d_strerror(rc).decode())
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    L.gs2d_image_free(p)
+    return out
+
+
+def load_image(path):
+    """Target ingest (Image2DRGBA8::load, prp.cpp:179-193): JPEG decoded with stb_image's arithmetic, or binary PPM.
+    -> uint8 [H, W, 4], A = 255. Host code (gs2d_jpeg.cpp), no GPU needed."""
+    p, w, h = C.POINTER(C.c_uint8)(), C.c_int(), C.c_int()
+    rc = load_library().gs2d_image_load_rgba8(os.fsencode(path), C.byref(p), C.byref(w), C.byref(h))
+    return _take_image(rc, p, w, h)
+
+
+def decode_jpeg(data):
+    """JPEG bytes -> uint8 [H, W, 4] (same decoder as load_image)."""
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(bytes(data))
+    p, w, h = C.POINTER(C.c_uint8)(), C.c_int(), C.c_int()
+    rc = load_library().gs2d_image_decode_jpeg_rgba8(buf, len(data), C.byref(p), C.byref(w), C.byref(h))
+    return _take_image(rc, p, w, h)
+
+
+def write_ppm(path, rgba32f):
+    """Headless stand-in for tex0->upload( image0 ) (main.cpp:794): 8-bit binary PPM of an RGBA float image."""
+    a = np.ascontiguousarray(rgba32f, np.float32)
+    assert a.ndim == 3 and a.shape[2] == 4
+    rc = load_library().gs2d_image_write_ppm(os.fsencode(path), _ptr(a), a.shape[1], a.shape[0])
+    if rc != GS2D_OK:
+        raise Gs2dError(rc, load_library().gs2d_strerror(rc).decode())
+
+
+OVERLAY_DTYPE = np.dtype([("center", "<f4", (2,)), ("axis0", "<f4", (2,)), ("axis1", "<f4", (2,)),
+                          ("half_extent", "<f4", (2,))])
+
+
+def overlay_geometry(splats, nvtx=16):
+    """The per-splat overlay main() draws (main.cpp:421-476) as data: (records [n] of OVERLAY_DTYPE, ellipse polylines
+    [n, nvtx + 1, 2]); image coordinates, y down."""
+    s = np.ascontiguousarray(splats, SPLAT_DTYPE)
+    out = np.zeros(len(s), OVERLAY_DTYPE)
+    ell = np.zeros((len(s), nvtx + 1, 2), np.float32)
+    rc = load_library().gs2d_overlay_geometry(_ptr(s), len(s), nvtx, _ptr(out), _ptr(ell))
+    if rc != GS2D_OK:
+        raise Gs2dError(rc, load_library().gs2d_strerror(rc).decode())
+    return out, ell
 
 
 def set_tuning(name, value):

@@ -176,6 +176,8 @@ extern "C" const char* gs2d_strerror( int code )
 	case GS2D_ERR_OOM: return "out of memory";
 	case GS2D_ERR_NCCL: return "NCCL unavailable or failed";
 	case GS2D_ERR_STATE: return "call sequence error";
+	case GS2D_ERR_IO: return "file could not be opened, read or written";
+	case GS2D_ERR_FORMAT: return "unsupported or mismatching file contents";
 	default: return "unknown error";
 	}
 }
@@ -538,7 +540,7 @@ extern "C" int gs2d_download_state( gs2d_ctx* c, int image, gs2d_splat* splats, 
 	int rc = resolve( c );
 	if( rc && rc != GS2D_ERR_NONFINITE )
 		return rc;
-	int rc2 = download_aos( c, image, splats, adam, nullptr );
+	int rc2 = ( splats || adam ) ? download_aos( c, image, splats, adam, nullptr ) : GS2D_OK;
 	if( rc2 )
 		return rc2;
 	if( beta1t )
@@ -555,6 +557,29 @@ extern "C" int gs2d_set_optimize_opacity( gs2d_ctx* c, int enabled )
 	if( !c )
 		return GS2D_ERR_INVALID;
 	c->hp.optimize_opacity = enabled ? 1 : 0;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_get_optimize_opacity( const gs2d_ctx* c, int* enabled )
+{
+	if( !c || !enabled )
+		return GS2D_ERR_INVALID;
+	*enabled = c->hp.optimize_opacity;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_get_dims( const gs2d_ctx* c, int* W, int* H, int* n_splats, int* n_images )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	if( W )
+		*W = c->g.W;
+	if( H )
+		*H = c->g.H;
+	if( n_splats )
+		*n_splats = c->g.n_splats;
+	if( n_images )
+		*n_images = c->g.n_images;
 	return GS2D_OK;
 }
 

@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 
 FLOP_FWD, FLOP_BWD = 27.0, 86.0  # per live (pixel, splat) pair, hoisted counts of SURVEY.md §8(d)
 ADAM_BYTES = 288.0               # per Gaussian: 8 planes x (p,g,m,v read + p,m,v,g write) + opacity plane p,g rw
+BIN_BYTES_PER_KEY = 26.0         # place + rank passes over the (tile, Gaussian) list entries, see run_ours
 SAMPLE_DIV = 16                  # CPU sample = 1/16 of the workload (same Gaussian density)
 
 
@@ -207,8 +208,21 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident run: `value` ---------------------------------------------------------------------------
+    # ---- counting pass (untimed): live (pixel, Gaussian) pairs and list entries of the SAME K iterations ---------
+    # The counting variant of the forward blend costs ~10 % (profiles/r1_ncu_blend_v4.txt), so the work counters the
+    # roofline needs are taken on an identical, untimed run of the same iterations and the timed run has them off.
     fit.step(max(W, 3))  # warm-up (>= 3), also grows the key buffers to their steady size
+    fit.set_stats(True)
+    fit.set_profiling(True)  # resets the running sums
+    fit.step(K, want_mse=False)
+    fit.sync()
+    stats = fit.stats()
+    fit.set_profiling(False)
+    fit.set_stats(False)
+    fit.restart()
+
+    # ---- device-resident run: `value` ---------------------------------------------------------------------------
+    fit.step(max(W, 3))
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -220,7 +234,6 @@ def run_ours(args):
     wall_ms = (time.perf_counter() - t0) * 1e3
     dev_ms = fit.last_step_ms()  # CUDA events on the library's stream around the K iterations
     prof, n_prof = fit.get_profile()
-    stats = fit.stats()  # running sums since set_profiling(True)
     fit.set_profiling(False)
     clocks = sampler.stop()
     launches = fit.launch_count() - launches0
@@ -272,12 +285,12 @@ def run_ours(args):
         kern["k_backward"] = {"ms": prof["backward"], "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
                               "unit": "TFLOP/s", "frac": a / fp32_peak}
     if prof["sort"] > 0:
-        tiles = ((S + 15) // 16) ** 2
-        passes = max(1, -(-max(1, (tiles - 1).bit_length()) // 8))
-        b = keys_per_it / world * (passes * 24.0 + 4.0)  # per pass: hist read 4 + scatter read 8 + write 8 (+4 vals)...
+        # k_scan_* + k_place + k_rank (gs2d_binning.cu): per list entry read the (bucket, splat, rank) triple (10 B) and
+        # the bucket offset (4 B), write the bucketed entry (4 B), read it back and write it in index order (8 B)
+        b = keys_per_it / world * BIN_BYTES_PER_KEY
         a = b / (prof["sort"] * 1e-3) / 1e9
-        kern["radix_sort"] = {"ms": prof["sort"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
-                              "frac": a / hbm_peak, "passes": passes}
+        kern["place_rank"] = {"ms": prof["sort"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": a / hbm_peak, "bytes_per_list_entry": BIN_BYTES_PER_KEY}
     if prof["adam"] > 0:
         a = ADAM_BYTES * N / (prof["adam"] * 1e-3) / 1e9
         kern["k_adam"] = {"ms": prof["adam"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",

@@ -35,7 +35,9 @@ enum
 	GS2D_ERR_NONFINITE = -4, /* non-aborting mirror of main.cpp:752-785 (colour, sx, sy, rot or pos.x not finite) */
 	GS2D_ERR_OOM = -5,       /* device or pinned allocation failed */
 	GS2D_ERR_NCCL = -6,      /* NCCL missing or a collective failed */
-	GS2D_ERR_STATE = -7      /* call sequence error (e.g. backward before forward) */
+	GS2D_ERR_STATE = -7,     /* call sequence error (e.g. backward before forward) */
+	GS2D_ERR_IO = -8,        /* file missing / unreadable / unwritable */
+	GS2D_ERR_FORMAT = -9     /* not a file this library understands, or it does not match the context */
 };
 
 /* == struct Splat, 36 bytes (main.cpp:85-93); also the layout of dSplats (main.cpp:550) */
@@ -120,6 +122,7 @@ int gs2d_download_state( gs2d_ctx* ctx, int image, gs2d_splat* splats, gs2d_spla
                          float* beta2t, int* iteration );
 
 int gs2d_set_optimize_opacity( gs2d_ctx* ctx, int enabled ); /* the ImGui checkbox, main.cpp:825 */
+int gs2d_get_optimize_opacity( const gs2d_ctx* ctx, int* enabled );
 
 /* n_iters full iterations (bin+sort, forward, backward, [allreduce], Adam), main.cpp:414-809.
  * mse: NULL => enqueue only (asynchronous); else n_iters*n_images doubles, mse[it*n_images+img] = the value the
@@ -167,6 +170,39 @@ int gs2d_set_stats( gs2d_ctx* ctx, int enable );
 int gs2d_launch_count( gs2d_ctx* ctx, uint64_t* n );
 
 int gs2d_sync( gs2d_ctx* ctx );
+
+/* Dimensions the context was created with (any pointer may be NULL). */
+int gs2d_get_dims( const gs2d_ctx* ctx, int* W, int* H, int* n_splats, int* n_images );
+
+/* ---- the steps either side of the path (host code, gs2d_io.cpp / gs2d_jpeg.cpp) -------------- */
+
+/* f3 — checkpoint = the reference's loop-carried state {splats, splatAdams, beta1t, beta2t, iterations}
+ * (main.cpp:271-278) of every image of the context, plus optimizeOpacity (main.cpp:317). The reference itself saves
+ * nothing; the file layout is documented in gs2d_io.cpp. Loading requires equal n_splats/n_images. */
+int gs2d_save_checkpoint( gs2d_ctx* ctx, const char* path );
+int gs2d_load_checkpoint( gs2d_ctx* ctx, const char* path );
+
+/* f2 — target ingest (prp.cpp:179-193): decode a JPEG (baseline or progressive Huffman, 8 bit, 1 or 3 components,
+ * any sampling factors) to RGBA8 with the same integer arithmetic as stb_image's decoder, which the reference uses
+ * through prlib (libs/prlib/libs/stb/stb_image.h): bit-identical pixels, A = 255. Binary PPM (P6, maxval 255) is
+ * accepted too. *rgba is malloc'ed; release it with gs2d_image_free. */
+int gs2d_image_load_rgba8( const char* path, uint8_t** rgba, int* W, int* H );
+int gs2d_image_decode_jpeg_rgba8( const uint8_t* bytes, size_t n_bytes, uint8_t** rgba, int* W, int* H );
+void gs2d_image_free( uint8_t* rgba );
+/* Headless stand-in for tex0->upload( image0 ) (main.cpp:794): round( clamp( c, 0, 1 ) * 255 ) as binary PPM. */
+int gs2d_image_write_ppm( const char* path, const float* rgba32f, int W, int H );
+
+/* f4 — the overlay main() draws per splat (main.cpp:421-476) as data: the two eigen-axes scaled by sqrt(lambda)
+ * (eignValues :187-196, eigen_vectors_of_cov :223-234), the nvtx-segment ellipse polyline (:453-461, prlib's
+ * CircleGenerator recurrence prp.hpp:276-313) and the exact half-extent of the 1-sigma bounding box (:464-465).
+ * y is image-down here (the reference flips it for GL). ellipse: n * (nvtx + 1) * 2 floats or NULL. */
+typedef struct gs2d_overlay
+{
+	float center[2];
+	float axis0[2], axis1[2]; /* eigenvector * sqrt(eigenvalue), axis0 = larger */
+	float half_extent[2];     /* sqrt( inv_cov[1][1] * det ), sqrt( inv_cov[0][0] * det ) */
+} gs2d_overlay;
+int gs2d_overlay_geometry( const gs2d_splat* splats, int n, int nvtx, gs2d_overlay* out, float* ellipse );
 
 /* Microbenchmarks that give the roofline denominators on the device at hand:
  * FP32 FMA issue rate (TFLOP/s, FMA = 2 flop) and HBM copy bandwidth (GB/s, read+write bytes). */

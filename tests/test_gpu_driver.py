@@ -1,0 +1,106 @@
+"""GPU tests of the SURVEY.md §8(f) rows around the hot path: the headless fit driver (f1) against the unmodified
+reference's stdout, and the checkpoint round trip (f3)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from gs2d_loader import ROOT, gs2d
+
+pytestmark = pytest.mark.gpu
+
+FIT = os.path.join(ROOT, "2dgaussiansplatting_b200", "gs2d_fit")
+
+
+def write_target_ppm(golden_dir, cfg, path):
+    rgb = np.load(os.path.join(golden_dir, f"{cfg}_target_rgb8.npz"))["rgb"]
+    h, w, _ = rgb.shape
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(rgb.tobytes())
+    return w, h
+
+
+def parse(lines):
+    out = []
+    for ln in lines:
+        a, b = ln.split(" itr, mse ")
+        out.append((int(a), float(b)))
+    return out
+
+
+def test_driver_stdout_equals_reference_stdout(golden_dir, tmp_path):
+    """`gs2d_fit target --iters 60` prints the lines the unmodified main.cpp prints (main.cpp:807), C1."""
+    ppm = str(tmp_path / "c1.ppm")
+    write_target_ppm(golden_dir, "c1", ppm)
+    out_ppm = str(tmp_path / "render.ppm")
+    csv = str(tmp_path / "overlay.csv")
+    r = subprocess.run([FIT, ppm, "--iters", "60", "--out", out_ppm, "--overlay", csv], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stderr
+    got = parse(r.stdout.strip().splitlines())
+    ref = parse(open(os.path.join(golden_dir, "c1_mse.txt")).read().strip().splitlines()[:60])
+    assert [g[0] for g in got] == list(range(60))
+    assert r.stdout.splitlines()[0] == open(os.path.join(golden_dir, "c1_mse.txt")).readline().rstrip("\n")
+    rel = np.array([abs(g[1] - e[1]) / e[1] for g, e in zip(got, ref)])
+    assert rel[:50].max() < 1e-4 and rel.max() < 2e-3, rel.max()
+    # the dumped render is the last iteration's image0 and the overlay has one row per splat
+    img = gs2d.load_image(out_ppm)
+    assert img.shape == (213, 268, 4) and img[..., :3].std() > 5
+    assert len(open(csv).read().strip().splitlines()) == 1 + 1024
+
+
+def test_driver_restart_and_opacity_events(golden_dir, tmp_path):
+    """The "Restart" button re-runs init(): the loss curve starts over; the opacity checkbox changes the fit."""
+    ppm = str(tmp_path / "c1.ppm")
+    write_target_ppm(golden_dir, "c1", ppm)
+    r = subprocess.run([FIT, ppm, "--iters", "12", "--restart-at", "6"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    got = parse(r.stdout.strip().splitlines())
+    assert [g[0] for g in got] == [0, 1, 2, 3, 4, 5, 0, 1, 2, 3, 4, 5]
+    assert got[6][1] == got[0][1] and abs(got[8][1] - got[2][1]) / got[2][1] < 1e-4
+    a = subprocess.run([FIT, ppm, "--iters", "12"], capture_output=True, text=True, timeout=300)
+    b = subprocess.run([FIT, ppm, "--iters", "12", "--opacity-from", "4"], capture_output=True, text=True, timeout=300)
+    la, lb = parse(a.stdout.strip().splitlines()), parse(b.stdout.strip().splitlines())
+    # identical up to and including the render of iteration 4 (its Adam step is the first one that moves opacity)
+    assert [x[1] for x in la[:5]] == pytest.approx([x[1] for x in lb[:5]], rel=1e-5)
+    assert abs(la[-1][1] - lb[-1][1]) / la[-1][1] > 1e-4
+
+
+def test_checkpoint_round_trip(golden_dir, tmp_path):
+    """save -> load into a fresh context restores {splats, splatAdams, beta1t, beta2t, iterations} bit for bit, and the
+    fit continues as if it had never stopped."""
+    rgb = np.load(os.path.join(golden_dir, "c1_target_rgb8.npz"))["rgb"]
+    h, w, _ = rgb.shape
+    rgba8 = np.concatenate([rgb, np.full((h, w, 1), 255, np.uint8)], axis=2)
+    ck = str(tmp_path / "state.gs2d")
+    with gs2d.Fitter(w, h, 1024) as fit:
+        fit.set_target_u8(rgba8)
+        fit.restart()
+        fit.optimize_opacity = True
+        fit.step(7)
+        fit.save_checkpoint(ck)
+        s0, a0, b1, b2, it = fit.download()
+        cont = fit.step(5)[:, 0]
+    assert os.path.getsize(ck) == 8 + 24 + 12 + 1024 * (36 + 72)
+    with gs2d.Fitter(w, h, 1024) as fit:
+        fit.set_target_u8(rgba8)
+        fit.load_checkpoint(ck)
+        s1, a1, c1, c2, it1 = fit.download()
+        assert s0.tobytes() == s1.tobytes() and a0.tobytes() == a1.tobytes()
+        assert (b1, b2, it) == (c1, c2, it1) and it1 == 7
+        import ctypes as C
+        flag = C.c_int(-1)
+        assert fit.lib.gs2d_get_optimize_opacity(fit._ctx, C.byref(flag)) == 0 and flag.value == 1  # restored
+        resumed = fit.step(5)[:, 0]
+    assert np.allclose(resumed, cont, rtol=1e-5)
+    # a checkpoint of another problem size is refused and leaves the context usable
+    with gs2d.Fitter(w, h, 512) as fit:
+        with pytest.raises(gs2d.Gs2dError) as e:
+            fit.load_checkpoint(ck)
+        assert e.value.code == -9
+    with gs2d.Fitter(w, h, 1024) as fit:
+        with pytest.raises(gs2d.Gs2dError) as e:
+            fit.load_checkpoint(str(tmp_path / "nope"))
+        assert e.value.code == -8
