@@ -211,24 +211,21 @@ static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
 	Buffers& b = c->b;
 	for( int i = 0; i < 2; i++ )
 	{
-		if( b.keys[i] )
-			cudaFree( b.keys[i] );
 		if( b.vals[i] )
 			cudaFree( b.vals[i] );
-		b.keys[i] = b.vals[i] = nullptr;
+		b.vals[i] = nullptr;
 	}
+	if( b.triples )
+		cudaFree( b.triples );
+	b.triples = nullptr;
 	if( b.cover )
 		cudaFree( b.cover );
 	b.cover = nullptr;
 	capacity = std::min<unsigned long long>( std::max<unsigned long long>( capacity, 1ull << 16 ), 0xFFFF0000ull );
-	CK( cudaMalloc( &b.keys[0], sizeof( unsigned ) * capacity ) );
+	CK( cudaMalloc( &b.triples, sizeof( unsigned long long ) * capacity ) );
 	CK( cudaMalloc( &b.vals[0], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.vals[1], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * 8 * capacity ) );
-	if( b.pair_rank )
-		cudaFree( b.pair_rank );
-	b.pair_rank = nullptr;
-	CK( cudaMalloc( &b.pair_rank, sizeof( unsigned short ) * capacity ) );
 	b.capacity = capacity;
 	return GS2D_OK;
 }
@@ -252,8 +249,8 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->comm && g_nccl.CommDestroy )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
-	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.pair_rank,
-	                 b.scan_sums,  b.keys[0], b.keys[1], b.vals[0],    b.vals[1],    b.cover, b.tile_range,
+	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
+	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage };
 	for( void* p : ptrs )

@@ -10,7 +10,7 @@
 //   k_preprocess   : covariance, inverse, row range (cov_of main.cpp:206-221, :432-436, :489-491) -> 64-byte record;
 //                    the tiles the 3-sigma ellipse can touch (per tile row: the x-extent of the ellipse inside the
 //                    band of that row's pixel centres, see tile_span) are emitted as unordered (bucket, splat, rank)
-//                    triples, rank = arrival order in the bucket. The bucket counters are 16 bits wide and the
+//                    triples packed into one 64-bit word, rank = arrival order in the bucket. The bucket counters are 16 bits wide and the
 //                    counters of 4 consecutive tiles share one 64-bit word, so ONE atomicAdd serves up to 4 tiles
 //                    of a tile row (the L2 atomic rate, not HBM, bounds this kernel).
 //   k_scan_*       : exclusive scan of the bucket counts in (tile, slice) order = bucket offsets; capacity check
@@ -75,21 +75,23 @@ struct SplatBin
 	int rtx0, rtx1, ty0, ty1;
 	int tile_base; // first tile id of the splat's image
 	int slice;     // index slice of the splat
+	int local;     // index of the splat inside its slice
 };
 
 #define BIG_RECT 1024 // rectangles with more tiles than this are binned by the whole warp
 
+// One emitted (tile, splat) pair is ONE 64-bit word: bucket = tile * n_slices + slice in the low half, then the
+// splat's index inside its slice (16 bits; slice_size <= 65535) and the arrival order inside the bucket (16 bits).
+// The image is implied by the tile and the slice by the bucket, so the global splat index is rebuilt from them.
 struct PairOut
 {
-	unsigned* bucket;            // tile * n_slices + slice
-	unsigned* splat;
-	unsigned short* rank;        // arrival order inside the bucket
+	unsigned long long* triple;  // bucket | local << 32 | rank << 48
 	unsigned long long* cnt64;   // [n_slices][nt_pad / 4] words of four 16-bit bucket counters (consecutive tiles)
 };
 
 // Emit the pairs of tiles id_lo..id_hi (one tile row of one splat) at pos.., one 64-bit atomic per 4-tile group.
 __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
-                                          int slice, unsigned splat, unsigned long long pos )
+                                          int slice, unsigned local, unsigned long long pos )
 {
 	unsigned long long* cnt = o.cnt64 + (size_t)slice * ( g.nt_pad >> 2 );
 	for( unsigned grp = id_lo >> 2; grp <= ( id_hi >> 2 ); grp++ )
@@ -100,9 +102,9 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 		const unsigned long long old = atomicAdd( cnt + grp, add );
 		for( unsigned f = f0; f <= f1; f++, pos++ )
 		{
-			o.bucket[pos] = ( grp * 4u + f ) * (unsigned)g.n_slices + (unsigned)slice;
-			o.splat[pos] = splat;
-			o.rank[pos] = (unsigned short)( old >> ( 16u * f ) );
+			const unsigned bucket = ( grp * 4u + f ) * (unsigned)g.n_slices + (unsigned)slice;
+			const unsigned long long rank = ( old >> ( 16u * f ) ) & 0xffffull;
+			__stcs( o.triple + pos, (unsigned long long)bucket | ( (unsigned long long)local << 32 ) | ( rank << 48 ) );
 		}
 	}
 }
@@ -121,6 +123,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 	sb.ty1 = 0;
 	sb.tile_base = 0;
 	sb.slice = 0;
+	sb.local = 0;
 	sb.k.begY = 1;
 	sb.k.endY = 0;
 	if( gi < g.n_total )
@@ -201,6 +204,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		const int img = gi / g.n_splats;
 		sb.tile_base = img * g.tiles_y * g.tiles_x;
 		sb.slice = ( gi - img * g.n_splats ) / g.slice_size;
+		sb.local = ( gi - img * g.n_splats ) - sb.slice * g.slice_size;
 		sb.k.px = px;
 		sb.k.py = py;
 		sb.k.a = a;
@@ -263,7 +267,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			if( !tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
 				continue;
 			const unsigned row = (unsigned)( sb.tile_base + ty * g.tiles_x );
-			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, sb.slice, (unsigned)gi, pos );
+			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, sb.slice, (unsigned)sb.local, pos );
 			pos += (unsigned)( hi - lo + 1 );
 		}
 	}
@@ -294,7 +298,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			if( pos + n > capacity )
 				continue;
 			const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, o.slice, (unsigned)gj, pos );
+			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, o.slice, (unsigned)o.local, pos );
 		}
 	}
 }
@@ -410,15 +414,45 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restri
 }
 
 // ------------------------------------------------------------------------------------------- place and order ---
-__global__ void __launch_bounds__( 256 ) k_place( PairOut in, const unsigned* __restrict__ offset,
-                                                  unsigned* __restrict__ list, const DevState* __restrict__ st )
+__device__ __forceinline__ unsigned splat_of_triple( const Geometry& g, unsigned bucket, unsigned local,
+                                                    unsigned tiles_per_image )
+{
+	const unsigned tile = bucket / (unsigned)g.n_slices, slice = bucket - tile * (unsigned)g.n_slices;
+	return ( tile / tiles_per_image ) * (unsigned)g.n_splats + slice * (unsigned)g.slice_size + local;
+}
+
+__global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned long long* __restrict__ triple,
+                                                  const unsigned* __restrict__ offset, unsigned* __restrict__ list,
+                                                  const DevState* __restrict__ st )
 {
 	if( st->need_capacity )
 		return;
 	const unsigned long long n = st->n_keys;
 	const unsigned long long stride = (unsigned long long)gridDim.x * 256;
-	for( unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride )
-		list[offset[in.bucket[i]] + in.rank[i]] = in.splat[i];
+	const unsigned tpi = (unsigned)( g.tiles_x * g.tiles_y );
+	unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x;
+	// four independent gather chains in flight per thread (the kernel is bound by the latency of its scattered accesses)
+	for( ; i + 3 * stride < n; i += 4 * stride )
+	{
+		unsigned long long t[4];
+		unsigned of[4];
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+			t[k] = __ldcs( triple + i + k * stride );
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+			of[k] = __ldg( offset + (unsigned)t[k] );
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+			list[of[k] + (unsigned)( t[k] >> 48 )] =
+			    splat_of_triple( g, (unsigned)t[k], (unsigned)( t[k] >> 32 ) & 0xffffu, tpi );
+	}
+	for( ; i < n; i += stride )
+	{
+		const unsigned long long t = triple[i];
+		list[offset[(unsigned)t] + (unsigned)( t >> 48 )] =
+		    splat_of_triple( g, (unsigned)t, (unsigned)( t >> 32 ) & 0xffffu, tpi );
+	}
 }
 
 // One thread per bucket: order its entries by splat index (rank by counting: the indices are unique), list -> out.
@@ -442,13 +476,32 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		tile_range[tile].y = start + n;
 	const unsigned* p = list + start;
 	unsigned* q = out + start;
-	if( n == 1 )
-		q[0] = p[0];
-	else if( n == 2 )
+	if( n <= 8u )
 	{
-		const unsigned x = p[0], y = p[1];
-		q[0] = min( x, y );
-		q[1] = max( x, y );
+		// the common case (3.3 entries on average): a fixed 19-comparator network over 8 registers padded with
+		// +inf - no data-dependent control flow, so the lanes of a warp (buckets of all sizes) stay converged
+		unsigned e[8];
+#pragma unroll
+		for( int a = 0; a < 8; a++ )
+			e[a] = (unsigned)a < n ? p[a] : 0xffffffffu;
+#define CE( x, y )                                                                                                    \
+	{                                                                                                                 \
+		const unsigned lo_ = min( e[x], e[y] ), hi_ = max( e[x], e[y] );                                              \
+		e[x] = lo_;                                                                                                   \
+		e[y] = hi_;                                                                                                   \
+	}
+		CE( 0, 1 ) CE( 2, 3 ) CE( 4, 5 ) CE( 6, 7 )
+		CE( 0, 2 ) CE( 1, 3 ) CE( 4, 6 ) CE( 5, 7 )
+		CE( 1, 2 ) CE( 5, 6 ) CE( 0, 4 ) CE( 3, 7 )
+		CE( 1, 5 ) CE( 2, 6 )
+		CE( 1, 4 ) CE( 3, 6 )
+		CE( 2, 4 ) CE( 3, 5 )
+		CE( 3, 4 )
+#undef CE
+#pragma unroll
+		for( int a = 0; a < 8; a++ )
+			if( (unsigned)a < n )
+				q[a] = e[a];
 	}
 	else
 		for( unsigned a = 0; a < n; a++ )
@@ -466,7 +519,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
                                cudaEvent_t after_emit )
 {
 	int launches = 0;
-	*sorted_buf = 0; // the ordered lists end up in vals[0] (the splat column of the triples is dead by then)
+	*sorted_buf = 0; // the ordered lists end up in vals[0]
 	cudaMemsetAsync( &b.state->n_keys, 0, 2 * sizeof( unsigned long long ), s );
 	if( g.n_total == 0 )
 	{
@@ -478,9 +531,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
 	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices, s );
 	PairOut po;
-	po.bucket = b.keys[0];
-	po.splat = b.vals[0];
-	po.rank = b.pair_rank;
+	po.triple = b.triples;
 	po.cnt64 = reinterpret_cast<unsigned long long*>( b.bucket_cnt );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
 	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
@@ -491,7 +542,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, nbk, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
 	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.bucket_off, nbk, b.scan_sums );
-	k_place<<<148 * 16, 256, 0, s>>>( po, b.bucket_off, b.vals[1], b.state );
+	k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.vals[1], b.state );
 	k_rank<<<( nbk + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.vals[1], b.vals[0], b.tile_range, nbk,
 	                                           b.state );
 	launches += 5;

@@ -161,9 +161,8 @@ struct Buffers
 	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
 	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
 	unsigned* scan_sums;        // scratch of the scan
-	unsigned* keys[2];          // keys[0]: bucket of the unordered (bucket, splat, rank) triples; keys[1] unused
-	unsigned* vals[2];          // vals[0]: splat of the triples, later the ordered lists; vals[1]: bucketed, unordered
-	unsigned short* pair_rank;  // arrival order of the triple inside its bucket
+	unsigned long long* triples; // [capacity] unordered (bucket, splat-in-slice, arrival rank) words, gs2d_binning.cu
+	unsigned* vals[2];          // vals[1]: the lists bucketed but unordered; vals[0]: ordered by splat index (final)
 	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward)
 	unsigned long long capacity;
 	uint2* tile_range;        // [n_tiles_total]
