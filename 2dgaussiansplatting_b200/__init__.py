@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
     "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
-    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
+    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
     "gs2d_image_load_rgba8", "gs2d_image_decode_jpeg_rgba8", "gs2d_image_free", "gs2d_image_write_ppm",
     "gs2d_overlay_geometry",
 ]
@@ -97,6 +97,7 @@ def load_library():
     L.gs2d_destroy.restype = None
     L.gs2d_set_target_rgba32f.argtypes = [vp, i, vp]
     L.gs2d_set_target_rgba8.argtypes = [vp, i, vp]
+    L.gs2d_set_target_rgba8_async.argtypes = [vp, i, vp]
     L.gs2d_init_reference.argtypes = [vp]
     L.gs2d_upload_state.argtypes = [vp, i, vp, vp, f, f, i]
     L.gs2d_download_state.argtypes = [vp, i, vp, vp, C.POINTER(f), C.POINTER(f), C.POINTER(i)]
@@ -196,6 +197,7 @@ class Fitter:
         self.lib = load_library()
         self.W, self.H, self.n_splats, self.n_images = int(W), int(H), int(n_splats), int(n_images)
         self._ctx = C.c_void_p()
+        self._rank, self._n_ranks = 0, 1
         self.params = params if params is not None else default_params()
         rc = self.lib.gs2d_create(C.byref(self._ctx), self.W, self.H, self.n_splats, self.n_images, int(device),
                                   C.byref(self.params))
@@ -341,6 +343,16 @@ class Fitter:
         """Target from a raw host pointer (e.g. a pinned torch tensor's data_ptr()): H*W*4 bytes RGBA8."""
         self._ck(self.lib.gs2d_set_target_rgba8(self._ctx, image, C.c_void_p(ptr)))
 
+    def set_target_u8_ptr_async(self, ptr, image=0):
+        """Non-blocking upload from PINNED host memory; takes effect at the next forward pass (double-buffered, so
+        the copy of the next target overlaps the iterations running on the current one)."""
+        self._ck(self.lib.gs2d_set_target_rgba8_async(self._ctx, image, C.c_void_p(ptr)))
+
+    def target_bytes_per_upload(self):
+        """Bytes one target upload moves on this context: the whole RGBA8 image, or this rank's band once sharded."""
+        t0, t1 = (0, (self.H + 15) // 16) if self._n_ranks == 1 else band_rows((self.H + 15) // 16, self._rank, self._n_ranks)
+        return (min(t1 * 16, self.H) - min(t0 * 16, self.H)) * self.W * 4
+
     def launch_count(self):
         n = C.c_uint64()
         self._ck(self.lib.gs2d_launch_count(self._ctx, C.byref(n)))
@@ -361,6 +373,7 @@ class Fitter:
     def comm_init(self, rank, n_ranks, unique_id):
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
         self._ck(self.lib.gs2d_comm_init(self._ctx, rank, n_ranks, buf))
+        self._rank, self._n_ranks = rank, n_ranks
 
 
 def _take_image(rc, p, w, h):

@@ -106,6 +106,16 @@ struct gs2d_ctx
 	size_t dstage_bytes = 0;
 	DevState* h_state = nullptr; // pinned mirror
 
+	// asynchronous target upload (gs2d_set_target_rgba8_async): H2D on its own stream into one of two device staging
+	// buffers; the u8 -> float conversion is enqueued on the main stream by the next forward (apply_pending_target)
+	cudaStream_t copy_stream = nullptr;
+	uint8_t* ustage[2] = { nullptr, nullptr };
+	size_t ustage_bytes = 0;
+	cudaEvent_t copy_done[2] = { nullptr, nullptr }, convert_done[2] = { nullptr, nullptr };
+	int ustage_next = 0;
+	int pending_buf = -1, pending_image = 0; // an uploaded target that has not been converted yet
+	size_t pending_px0 = 0, pending_npx = 0;
+
 	long long expected_iteration = 0; // what the device counter will read once everything enqueued has run
 	cudaEvent_t ev[10]{};
 	float last_ms = 0.0f;
@@ -256,6 +266,20 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
+	for( int k = 0; k < 2; k++ )
+	{
+		if( c->ustage[k] )
+			cudaFree( c->ustage[k] );
+		if( c->copy_done[k] )
+			cudaEventDestroy( c->copy_done[k] );
+		if( c->convert_done[k] )
+			cudaEventDestroy( c->convert_done[k] );
+	}
+	if( c->copy_stream )
+	{
+		cudaStreamSynchronize( c->copy_stream );
+		cudaStreamDestroy( c->copy_stream );
+	}
 	if( c->pinned )
 		cudaFreeHost( c->pinned );
 	if( c->h_state )
@@ -405,13 +429,18 @@ static const void* h2d_source( gs2d_ctx* c, const void* user, size_t bytes )
 	return c->pinned;
 }
 
+static int apply_pending_target( gs2d_ctx* c );
+
 extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgba )
 {
 	if( !c || !rgba || image < 0 || image >= c->g.n_images )
 		return GS2D_ERR_INVALID;
 	CK( cudaSetDevice( c->device ) );
 	const size_t n_px = (size_t)c->g.W * c->g.H, bytes = n_px * sizeof( float4 );
-	int rc = ensure_staging( c, bytes );
+	int rc = apply_pending_target( c );
+	if( rc )
+		return rc;
+	rc = ensure_staging( c, bytes );
 	if( rc )
 		return rc;
 	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice,
@@ -420,19 +449,112 @@ extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgb
 	return GS2D_OK;
 }
 
+// Pixel range [px0, px0 + npx) of an image this context needs: all of it, or - once a communicator shards the image
+// into tile-row bands (gs2d_comm_init) - only the rows of this rank's band; the blend kernels read nothing else.
+static void target_rows( const gs2d_ctx* c, size_t* px0, size_t* npx )
+{
+	int y0 = 0, y1 = c->g.H;
+	if( c->comm && c->n_ranks > 1 )
+	{
+		y0 = std::min( c->g.band_ty0 * GS2D_TILE, c->g.H );
+		y1 = std::min( c->g.band_ty1 * GS2D_TILE, c->g.H );
+	}
+	*px0 = (size_t)y0 * c->g.W;
+	*npx = (size_t)( y1 - y0 ) * c->g.W;
+}
+
+// enqueue the conversion of an asynchronously uploaded target on the main stream (before the next forward)
+static int apply_pending_target( gs2d_ctx* c )
+{
+	if( c->pending_buf < 0 )
+		return GS2D_OK;
+	const int k = c->pending_buf;
+	c->pending_buf = -1;
+	CK( cudaStreamWaitEvent( c->stream, c->copy_done[k], 0 ) );
+	if( c->pending_npx )
+		c->launches += launch_u8_to_target( c->ustage[k],
+		                                    c->b.target + (size_t)c->pending_image * c->g.W * c->g.H + c->pending_px0,
+		                                    c->pending_npx, c->stream );
+	CK( cudaEventRecord( c->convert_done[k], c->stream ) );
+	return check_launch( c );
+}
+
 extern "C" int gs2d_set_target_rgba8( gs2d_ctx* c, int image, const uint8_t* rgba )
 {
 	if( !c || !rgba || image < 0 || image >= c->g.n_images )
 		return GS2D_ERR_INVALID;
 	CK( cudaSetDevice( c->device ) );
-	const size_t n_px = (size_t)c->g.W * c->g.H, bytes = n_px * 4;
-	int rc = ensure_staging( c, bytes );
+	int rc = apply_pending_target( c ); // keep the order of uploads
 	if( rc )
 		return rc;
-	CK( cudaMemcpyAsync( c->dstage, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice, c->stream ) );
-	c->launches += launch_u8_to_target( (const uint8_t*)c->dstage, c->b.target + (size_t)image * n_px, n_px, c->stream );
+	size_t px0, npx;
+	target_rows( c, &px0, &npx );
+	const size_t bytes = npx * 4;
+	rc = ensure_staging( c, std::max<size_t>( bytes, 16 ) );
+	if( rc )
+		return rc;
+	if( npx )
+	{
+		CK( cudaMemcpyAsync( c->dstage, h2d_source( c, rgba + px0 * 4, bytes ), bytes, cudaMemcpyHostToDevice, c->stream ) );
+		c->launches += launch_u8_to_target( (const uint8_t*)c->dstage,
+		                                    c->b.target + (size_t)image * c->g.W * c->g.H + px0, npx, c->stream );
+	}
 	CK( cudaStreamSynchronize( c->stream ) );
 	return check_launch( c );
+}
+
+extern "C" int gs2d_set_target_rgba8_async( gs2d_ctx* c, int image, const uint8_t* rgba )
+{
+	if( !c || !rgba || image < 0 || image >= c->g.n_images )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	cudaPointerAttributes attr;
+	if( cudaPointerGetAttributes( &attr, rgba ) != cudaSuccess || attr.type != cudaMemoryTypeHost )
+	{
+		cudaGetLastError();
+		return GS2D_ERR_INVALID; // an asynchronous copy needs page-locked memory; use gs2d_set_target_rgba8 otherwise
+	}
+	int rc = apply_pending_target( c ); // at most one unconverted upload: an older one takes effect first
+	if( rc )
+		return rc;
+	if( !c->copy_stream )
+	{
+		CK( cudaStreamCreateWithFlags( &c->copy_stream, cudaStreamNonBlocking ) );
+		for( int k = 0; k < 2; k++ )
+		{
+			CK( cudaEventCreateWithFlags( &c->copy_done[k], cudaEventDisableTiming ) );
+			CK( cudaEventCreateWithFlags( &c->convert_done[k], cudaEventDisableTiming ) );
+		}
+	}
+	size_t px0, npx;
+	target_rows( c, &px0, &npx );
+	const size_t bytes = npx * 4, full = (size_t)c->g.W * c->g.H * 4;
+	if( c->ustage_bytes < full )
+	{
+		CK( cudaStreamSynchronize( c->copy_stream ) );
+		CK( cudaStreamSynchronize( c->stream ) );
+		for( int k = 0; k < 2; k++ )
+		{
+			if( c->ustage[k] )
+				cudaFree( c->ustage[k] );
+			c->ustage[k] = nullptr;
+			CK( cudaMalloc( &c->ustage[k], full ) );
+			CK( cudaEventRecord( c->convert_done[k], c->stream ) );
+		}
+		c->ustage_bytes = full;
+	}
+	const int k = c->ustage_next;
+	c->ustage_next ^= 1;
+	// the buffer is free once the conversion that last read it has run
+	CK( cudaStreamWaitEvent( c->copy_stream, c->convert_done[k], 0 ) );
+	if( bytes )
+		CK( cudaMemcpyAsync( c->ustage[k], rgba + px0 * 4, bytes, cudaMemcpyHostToDevice, c->copy_stream ) );
+	CK( cudaEventRecord( c->copy_done[k], c->copy_stream ) );
+	c->pending_buf = k;
+	c->pending_image = image;
+	c->pending_px0 = px0;
+	c->pending_npx = npx;
+	return GS2D_OK;
 }
 
 static int write_state( gs2d_ctx* c, float b1t, float b2t, int iteration )
@@ -583,6 +705,9 @@ extern "C" int gs2d_get_dims( const gs2d_ctx* c, int* W, int* H, int* n_splats, 
 // ---- the iteration ----------------------------------------------------------------------------------------------
 static int enqueue_forward( gs2d_ctx* c )
 {
+	int rcp = apply_pending_target( c );
+	if( rcp )
+		return rcp;
 	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr );
 	c->launches += launch_forward( c->g, c->b, c->sorted_buf, true, c->stream );
 	c->launches += launch_finalize_loss( c->g, c->b, c->stream );
@@ -611,6 +736,9 @@ static int enqueue_allreduce( gs2d_ctx* c )
 static int enqueue_iteration( gs2d_ctx* c )
 {
 	cudaStream_t s = c->stream;
+	int rcp = apply_pending_target( c );
+	if( rcp )
+		return rcp;
 	gs2d_ctx::ProfRec* pr = nullptr;
 	if( c->profiling )
 	{
@@ -833,7 +961,10 @@ extern "C" int gs2d_last_mse( gs2d_ctx* c, double* mse )
 	if( !c || !mse )
 		return GS2D_ERR_INVALID;
 	CK( cudaSetDevice( c->device ) );
-	int rc = ensure_staging( c, sizeof( double ) * ( (size_t)c->g.n_images + 1 ) );
+	int rc = resolve( c ); // everything enqueued has run (re-running iterations skipped for lack of list capacity)
+	if( rc && rc != GS2D_ERR_NONFINITE )
+		return rc;
+	rc = ensure_staging( c, sizeof( double ) * ( (size_t)c->g.n_images + 1 ) );
 	if( rc )
 		return rc;
 	CK( cudaMemcpyAsync( c->pinned, c->b.loss, sizeof( double ) * c->g.n_images, cudaMemcpyDeviceToHost, c->stream ) );

@@ -109,6 +109,12 @@ void gs2d_destroy( gs2d_ctx* ctx );
 int gs2d_set_target_rgba32f( gs2d_ctx* ctx, int image, const float* rgba );
 /* Target from 8-bit RGBA as decoded by stb (prp.cpp:185): converted on device as u8/255.0f (prp.cpp:796-807). */
 int gs2d_set_target_rgba8( gs2d_ctx* ctx, int image, const uint8_t* rgba );
+/* The same without blocking: rgba must be page-locked host memory (else GS2D_ERR_INVALID) and stay untouched until the
+ * next gs2d_step / gs2d_forward / gs2d_sync has been issued. The copy runs on its own stream into one of two staging
+ * buffers, so the upload of the NEXT target overlaps the iterations still running on the current one; the new target
+ * takes effect at the next forward pass. Once gs2d_comm_init has sharded the image, both calls upload only the rows
+ * of this rank's band (the other rows of the buffer are not read). */
+int gs2d_set_target_rgba8_async( gs2d_ctx* ctx, int image, const uint8_t* rgba );
 
 /* init() of the reference (main.cpp:280-305) evaluated on the device for every image; resets Adam moments,
  * beta powers and the iteration counter ("Restart" button, main.cpp:828-831). */

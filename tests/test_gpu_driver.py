@@ -104,3 +104,40 @@ def test_checkpoint_round_trip(golden_dir, tmp_path):
         with pytest.raises(gs2d.Gs2dError) as e:
             fit.load_checkpoint(str(tmp_path / "nope"))
         assert e.value.code == -8
+
+
+def test_async_target_upload_equals_blocking():
+    """gs2d_set_target_rgba8_async (copy stream + two staging buffers, applied at the next forward) gives the same fit
+    as the blocking upload, keeps the order of back-to-back uploads, and refuses pageable memory."""
+    import torch
+
+    W, H, N = 200, 150, 300
+    rng = np.random.default_rng(5)
+    t = [rng.integers(0, 256, (H, W, 4), dtype=np.uint8) for _ in range(3)]
+    pin = [torch.from_numpy(x.copy()).pin_memory() for x in t]
+    with gs2d.Fitter(W, H, N) as a, gs2d.Fitter(W, H, N) as b:
+        a.set_target_u8(t[0])
+        a.restart()
+        ma = [a.step(2)[-1, 0]]
+        a.set_target_u8(t[2])
+        ma.append(a.step(2)[-1, 0])
+        b.set_target_u8_ptr_async(pin[0].data_ptr())
+        b.restart()
+        b.step(2, want_mse=False)
+        mb = [b.last_mse()[0]]
+        b.set_target_u8_ptr_async(pin[1].data_ptr())  # superseded by the next upload before any forward
+        b.set_target_u8_ptr_async(pin[2].data_ptr())
+        b.step(2, want_mse=False)
+        mb.append(b.last_mse()[0])
+        assert np.allclose(ma, mb, rtol=1e-6), (ma, mb)
+        assert ma[0] != ma[1]
+        with pytest.raises(gs2d.Gs2dError) as e:
+            b.set_target_u8_ptr_async(t[0].ctypes.data)
+        assert e.value.code == -1
+        # a blocking upload issued while an asynchronous one is pending comes later and wins
+        b.set_target_u8_ptr_async(pin[1].data_ptr())
+        b.set_target_u8(t[0])
+        b.restart()
+        a.set_target_u8(t[0])
+        a.restart()
+        assert np.allclose(a.step(1), b.step(1), rtol=1e-9)

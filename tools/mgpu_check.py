@@ -13,12 +13,12 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 W, H, N, ITERS = 700, 520, 6000, 12
-target = gs2d.synth_target(W, H, seed=3)
+target = np.rint(gs2d.synth_target(W, H, seed=3) * 255.0).astype(np.uint8)  # RGBA8: band-restricted upload path
 box = [gs2d.comm_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(box, src=0)
 with gs2d.Fitter(W, H, N, device=local) as fit:
     fit.comm_init(rank, world, box[0])
-    fit.set_target(target)
+    fit.set_target_u8(target)
     fit.restart()
     mse_n = fit.step(ITERS)[:, 0]
     s_n = fit.download()[0]
@@ -26,7 +26,7 @@ with gs2d.Fitter(W, H, N, device=local) as fit:
 ok = True
 if rank == 0:
     with gs2d.Fitter(W, H, N, device=local) as fit:
-        fit.set_target(target)
+        fit.set_target_u8(target)
         fit.restart()
         mse_1 = fit.step(ITERS)[:, 0]
         s_1 = fit.download()[0]
