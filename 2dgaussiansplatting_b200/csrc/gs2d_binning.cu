@@ -316,11 +316,12 @@ __device__ __forceinline__ unsigned bucket_count( const Geometry& g, const unsig
 
 // offset[i] = block-local exclusive scan of the bucket counts; sums[block] = block total
 __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( Geometry g, const unsigned short* __restrict__ cnt16,
-                                                                unsigned* __restrict__ offset, unsigned n,
-                                                                unsigned* __restrict__ sums )
+                                                                unsigned* __restrict__ offset, unsigned base,
+                                                                unsigned n, unsigned* __restrict__ sums )
 {
+	// scans the bucket window [base, n): the buckets of this rank's band of tile rows
 	__shared__ unsigned wtot[SCAN_THREADS / 32];
-	const unsigned i0 = blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
+	const unsigned i0 = base + blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
 	unsigned v[4];
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
@@ -402,11 +403,11 @@ __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ su
 		__syncthreads();
 	}
 }
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ offset, unsigned n,
-                                                              const unsigned* __restrict__ sums )
+__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ offset, unsigned base,
+                                                              unsigned n, const unsigned* __restrict__ sums )
 {
 	const unsigned add = sums[blockIdx.x];
-	const unsigned i0 = blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
+	const unsigned i0 = base + blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
 		if( i0 + k < n )
@@ -459,12 +460,12 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
 __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned short* __restrict__ cnt16,
                                                  const unsigned* __restrict__ offset,
                                                  const unsigned* __restrict__ list, unsigned* __restrict__ out,
-                                                 uint2* __restrict__ tile_range, unsigned n_buckets,
+                                                 uint2* __restrict__ tile_range, unsigned base, unsigned n_buckets,
                                                  const DevState* __restrict__ st )
 {
 	if( st->need_capacity )
 		return;
-	const unsigned i = blockIdx.x * 256 + threadIdx.x;
+	const unsigned i = base + blockIdx.x * 256 + threadIdx.x;
 	if( i >= n_buckets )
 		return;
 	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
@@ -538,13 +539,22 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
-	const unsigned scan_nb = ( nbk + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
-	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, nbk, b.scan_sums );
+	// only the buckets of this rank's band of tile rows hold entries (one contiguous window for a single image)
+	unsigned lo = 0, hi = nbk;
+	if( g.n_images == 1 )
+	{
+		lo = (unsigned)g.band_ty0 * (unsigned)g.tiles_x * (unsigned)g.n_slices;
+		hi = (unsigned)g.band_ty1 * (unsigned)g.tiles_x * (unsigned)g.n_slices;
+	}
+	if( hi <= lo )
+		return launches;
+	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, lo, hi, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
-	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.bucket_off, nbk, b.scan_sums );
+	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.bucket_off, lo, hi, b.scan_sums );
 	k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.vals[1], b.state );
-	k_rank<<<( nbk + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.vals[1], b.vals[0], b.tile_range, nbk,
-	                                           b.state );
+	k_rank<<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.vals[1], b.vals[0], b.tile_range, lo,
+	                                               hi, b.state );
 	launches += 5;
 	return launches;
 }

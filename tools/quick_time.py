@@ -15,6 +15,9 @@ with gs2d.Fitter(S, S, N, n_images=B) as fit:
     for i in range(B):
         fit.set_target_u8(tgt, image=i)
     fit.restart()
+    if os.environ.get('GS2D_BAND'):  # "r/n": time one rank's band of an n-rank run on a single GPU (no all-reduce)
+        r, n = map(int, os.environ['GS2D_BAND'].split('/'))
+        fit.set_band(r, n)
     fit.step(3)
     fit.set_profiling(True)
     fit.set_stats(os.environ.get('GS2D_STATS', '1') != '0')
