@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
     "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
-    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
+    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_comm_mode", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
     "gs2d_image_load_rgba8", "gs2d_image_decode_jpeg_rgba8", "gs2d_image_free", "gs2d_image_write_ppm",
     "gs2d_overlay_geometry",
 ]
@@ -113,6 +113,7 @@ def load_library():
     L.gs2d_comm_unique_id.argtypes = [vp]
     L.gs2d_comm_init.argtypes = [vp, i, i, vp]
     L.gs2d_set_band.argtypes = [vp, i, i]
+    L.gs2d_comm_mode.argtypes = [vp, C.POINTER(i), C.POINTER(i)]
     L.gs2d_last_step_ms.argtypes = [vp, C.POINTER(f)]
     L.gs2d_profile_step.argtypes = [vp, C.POINTER(f * 6)]
     L.gs2d_set_profiling.argtypes = [vp, i]
@@ -374,6 +375,13 @@ class Fitter:
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
         self._ck(self.lib.gs2d_comm_init(self._ctx, rank, n_ranks, buf))
         self._rank, self._n_ranks = rank, n_ranks
+
+    def comm_mode(self):
+        """-> (n_ranks, peer_memory): peer_memory is True when the gradient exchange is the fused reduce + Adam +
+        broadcast kernel over NVLink peer memory, False when it is the NCCL all-reduce."""
+        n, p = C.c_int(), C.c_int()
+        self._ck(self.lib.gs2d_comm_mode(self._ctx, C.byref(n), C.byref(p)))
+        return n.value, bool(p.value)
 
 
 def _take_image(rc, p, w, h):

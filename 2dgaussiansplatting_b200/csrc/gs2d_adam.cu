@@ -148,6 +148,111 @@ __global__ void __launch_bounds__( 256 ) k_adam( Geometry g, float* __restrict__
 		atomicOr( &st->nonfinite, 1 );
 }
 
+// ---------------------------------------------------------------------------------- Adam over peer memory ------
+// 128-bit load that is never served from a non-coherent cache: the peers' gradient planes were written by their
+// backward kernels (red.global.add in the home GPU's L2) and are read here over NVLink.
+__device__ __forceinline__ float4 ld_sys4( const float* p )
+{
+	float4 v;
+	asm volatile( "ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+	              : "=f"( v.x ), "=f"( v.y ), "=f"( v.z ), "=f"( v.w )
+	              : "l"( p ) );
+	return v;
+}
+
+// Reduce-scatter + Adam + all-gather in ONE kernel (the exchange step of the band-sharded fit): one
+// thread per (plane, quad) of the slice this rank owns (blockIdx.y = plane: the planes are independent scalars, and
+// nine times more threads keep nine times more NVLink loads in flight). NR = number of ranks (compile time, so that
+// the peer pointers live in registers and all NR loads are issued before the first add). Gradients are summed in
+// rank order (deterministic), and every splat is updated by exactly one rank, so the replicated parameters stay
+// bit-identical on all ranks.
+template <int NR>
+__global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, float* __restrict__ adam_m,
+                                                      float* __restrict__ adam_v, gs2d_params hp,
+                                                      const double* __restrict__ loss, DevState* st, int q0, int q1 )
+{
+	if( loss[g.n_images] != 0.0 )
+		return;
+	const int q = q0 + blockIdx.x * 128 + threadIdx.x;
+	if( q >= q1 )
+		return;
+	const int i4 = q * 4;
+	const int pl = blockIdx.y;
+	const size_t o = (size_t)pl * g.n_pad + i4;
+	const bool optimised = pl != PL_OP || hp.optimize_opacity;
+	float gv[4] = { 0.f, 0.f, 0.f, 0.f };
+	if( optimised )
+	{
+		if( pp.sum_all )
+		{
+			float4 part[NR];
+#pragma unroll
+			for( int r = 0; r < NR; r++ )
+				part[r] = ld_sys4( pp.grads[r] + o ); // NR loads in flight
+#pragma unroll
+			for( int r = 0; r < NR; r++ )
+			{
+				gv[0] = xadd( gv[0], part[r].x );
+				gv[1] = xadd( gv[1], part[r].y );
+				gv[2] = xadd( gv[2], part[r].z );
+				gv[3] = xadd( gv[3], part[r].w );
+			}
+		}
+		else
+		{
+			const float4 t = ld_sys4( pp.grads[pp.rank] + o );
+			gv[0] = t.x, gv[1] = t.y, gv[2] = t.z, gv[3] = t.w;
+		}
+	}
+	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
+	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
+	const float4 p = *reinterpret_cast<const float4*>( pp.params[pp.rank] + o );
+	float pv[4] = { p.x, p.y, p.z, p.w };
+	if( optimised )
+	{
+		float4 m = *reinterpret_cast<float4*>( adam_m + o );
+		float4 v = *reinterpret_cast<float4*>( adam_v + o );
+		float mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+			pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
+		*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
+		*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
+	}
+	bool bad = false;
+#pragma unroll
+	for( int k = 0; k < 4; k++ )
+	{
+		float x = pv[k];
+		if( pl == PL_PX )
+			x = clamp_glm( x, 0.0f, wmax );
+		else if( pl == PL_PY )
+			x = clamp_glm( x, 0.0f, hmax );
+		else if( pl == PL_SX || pl == PL_SY )
+			x = clamp_glm( x, hp.s_min, hp.s_max );
+		else if( pl == PL_CR || pl == PL_CG || pl == PL_CB )
+			x = clamp_glm( x, 0.0f, 1.0f );
+		else if( pl == PL_OP )
+			x = clamp_glm( x, hp.o_min, hp.o_max );
+		pv[k] = x;
+		if( pl != PL_PY && pl != PL_OP && i4 + k < g.n_total && !isfinite( x ) )
+			bad = true;
+	}
+	const float4 out = make_float4( pv[0], pv[1], pv[2], pv[3] );
+	// a parameter that cannot have changed (opacity while it is not optimised and already inside its clamp) is not sent
+	const bool changed = optimised || out.x != p.x || out.y != p.y || out.z != p.z || out.w != p.w;
+	if( changed )
+	{
+#pragma unroll
+		for( int r = 0; r < NR; r++ )
+			*reinterpret_cast<float4*>( pp.params[r] + o ) = out;
+	}
+	if( bad )
+		atomicOr( &st->nonfinite, 1 );
+	// the stores into the peers' planes are ordered before whatever this rank publishes next (the flag all-reduce)
+	asm volatile( "fence.acq_rel.sys;" ::: "memory" );
+}
+
 // ------------------------------------------------------------------------------------------------------ init ---
 __device__ __forceinline__ void pcg3d( unsigned& x, unsigned& y, unsigned& z ) // main.cpp:17-24
 {
@@ -284,6 +389,24 @@ int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cuda
 		return 0;
 	const int n4 = ( g.n_total + 3 ) / 4;
 	k_adam<<<( n4 + 255 ) / 256, 256, 0, s>>>( g, b.params, b.grads, b.adam_m, b.adam_v, p, b.loss, b.state );
+	return 1;
+}
+int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p, const PeerPtrs& pp, int q0, int q1,
+                      cudaStream_t s )
+{
+	if( q1 <= q0 )
+		return 0;
+	const dim3 grid( ( q1 - q0 + 127 ) / 128, GS2D_NPLANES );
+#define PEER_CASE( NR )                                                                                               \
+	case NR: k_adam_peer<NR><<<grid, 128, 0, s>>>( g, pp, b.adam_m, b.adam_v, p, b.loss, b.state, q0, q1 ); break;
+	switch( pp.n_ranks )
+	{
+		PEER_CASE( 2 ) PEER_CASE( 3 ) PEER_CASE( 4 ) PEER_CASE( 5 ) PEER_CASE( 6 ) PEER_CASE( 7 ) PEER_CASE( 8 )
+		PEER_CASE( 9 ) PEER_CASE( 10 ) PEER_CASE( 11 ) PEER_CASE( 12 ) PEER_CASE( 13 ) PEER_CASE( 14 ) PEER_CASE( 15 )
+		PEER_CASE( 16 )
+	default: return 0;
+	}
+#undef PEER_CASE
 	return 1;
 }
 int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,

@@ -27,6 +27,7 @@ struct NcclApi
 	int ( *CommInitRank )( ncclComm_t*, int, ncclUniqueId_, int ) = nullptr;
 	int ( *CommDestroy )( ncclComm_t ) = nullptr;
 	int ( *AllReduce )( const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t ) = nullptr;
+	int ( *AllGather )( const void*, void*, size_t, int, ncclComm_t, cudaStream_t ) = nullptr;
 	int ( *GroupStart )() = nullptr;
 	int ( *GroupEnd )() = nullptr;
 	const char* ( *GetErrorString )( int ) = nullptr;
@@ -48,6 +49,8 @@ static bool nccl_load()
 	g_nccl.CommDestroy = (int ( * )( ncclComm_t ))dlsym( h, "ncclCommDestroy" );
 	g_nccl.AllReduce =
 	    (int ( * )( const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t ))dlsym( h, "ncclAllReduce" );
+	g_nccl.AllGather =
+	    (int ( * )( const void*, void*, size_t, int, ncclComm_t, cudaStream_t ))dlsym( h, "ncclAllGather" );
 	g_nccl.GroupStart = (int ( * )())dlsym( h, "ncclGroupStart" );
 	g_nccl.GroupEnd = (int ( * )())dlsym( h, "ncclGroupEnd" );
 	g_nccl.GetErrorString = (const char* ( * )( int ))dlsym( h, "ncclGetErrorString" );
@@ -58,9 +61,13 @@ static bool nccl_load()
 }
 enum
 {
+	NCCL_UINT8 = 1,
+	NCCL_INT32 = 2,
 	NCCL_FLOAT32 = 7,
 	NCCL_FLOAT64 = 8,
-	NCCL_SUM = 0
+	NCCL_SUM = 0,
+	NCCL_MAX = 2,
+	NCCL_MIN = 3
 };
 
 static std::map<std::string, int>& tune_cache()
@@ -122,6 +129,17 @@ struct gs2d_ctx
 
 	ncclComm_t comm = nullptr;
 	int rank = 0, n_ranks = 1;
+	// peer-memory update (setup_peer_update): the other ranks' gradient / parameter / moment planes mapped through
+	// CUDA IPC; this rank owns the quads [own_q0, own_q1) of every plane (Adam moments are valid only there)
+	bool peer_update = false;
+	PeerPtrs peers{};
+	float* peer_m[GS2D_MAX_RANKS] = {};
+	float* peer_v[GS2D_MAX_RANKS] = {};
+	std::vector<void*> ipc_opened;
+	int own_q0 = 0, own_q1 = 0;
+	// developer timing of the pieces of the peer-memory update (GS2D_PEER_DEBUG=1): events around barrier 1, the
+	// fused kernel, barrier 2 and the gradient clear of every iteration; averages are printed by gs2d_destroy
+	std::vector<cudaEvent_t> dbg_ev;
 
 	// per-iteration CUDA-event profiling (gs2d_set_profiling): 7 events per enqueued iteration
 	struct ProfRec
@@ -193,6 +211,19 @@ extern "C" const char* gs2d_strerror( int code )
 }
 extern "C" const char* gs2d_last_error( const gs2d_ctx* c ) { return c ? c->err : ""; }
 
+static void owned_quads( const gs2d_ctx* c, int r, int* q0, int* q1 )
+{
+	const int n4 = c->g.n_pad / 4, per = ( n4 + c->n_ranks - 1 ) / c->n_ranks;
+	*q0 = std::min( r * per, n4 );
+	*q1 = std::min( ( r + 1 ) * per, n4 );
+}
+
+static int nccl_fail( gs2d_ctx* c, const char* what, int e )
+{
+	snprintf( c->err, sizeof( c->err ), "%s failed: %s", what, g_nccl.GetErrorString ? g_nccl.GetErrorString( e ) : "?" );
+	return GS2D_ERR_NCCL;
+}
+
 static int ensure_staging( gs2d_ctx* c, size_t bytes )
 {
 	if( bytes > c->pinned_bytes )
@@ -256,6 +287,26 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	cudaSetDevice( c->device );
 	if( c->stream )
 		cudaStreamSynchronize( c->stream );
+	if( !c->dbg_ev.empty() )
+	{
+		double sum[4] = { 0, 0, 0, 0 };
+		size_t n = c->dbg_ev.size() / 5, skip = n > 20 ? 10 : 0;
+		for( size_t i = skip; i < n; i++ )
+			for( int k = 0; k < 4; k++ )
+			{
+				float ms = 0;
+				cudaEventElapsedTime( &ms, c->dbg_ev[i * 5 + k], c->dbg_ev[i * 5 + k + 1] );
+				sum[k] += ms;
+			}
+		fprintf( stderr, "[gs2d rank %d] peer update over %zu iterations: barrier1 %.1f us, advance+fused kernel %.1f us, "
+		                 "barrier2 %.1f us, clear %.1f us\n",
+		         c->rank, n - skip, 1e3 * sum[0] / ( n - skip ), 1e3 * sum[1] / ( n - skip ), 1e3 * sum[2] / ( n - skip ),
+		         1e3 * sum[3] / ( n - skip ) );
+		for( cudaEvent_t e : c->dbg_ev )
+			cudaEventDestroy( e );
+	}
+	for( void* p : c->ipc_opened )
+		cudaIpcCloseMemHandle( p );
 	if( c->comm && g_nccl.CommDestroy )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
@@ -659,6 +710,24 @@ extern "C" int gs2d_download_state( gs2d_ctx* c, int image, gs2d_splat* splats, 
 	int rc = resolve( c );
 	if( rc && rc != GS2D_ERR_NONFINITE )
 		return rc;
+	if( adam && c->comm && c->peer_update )
+	{
+		// the Adam moments of a slice live on the rank that owns it: fetch the other slices over NVLink. The peers are
+		// quiescent: they cannot start their next update before this rank joins the next iteration's all-reduce.
+		for( int r = 0; r < c->n_ranks; r++ )
+		{
+			int q0, q1;
+			owned_quads( c, r, &q0, &q1 );
+			if( r == c->rank || q1 <= q0 )
+				continue;
+			for( int pl = 0; pl < GS2D_NPLANES; pl++ )
+			{
+				const size_t o = (size_t)pl * c->g.n_pad + (size_t)q0 * 4, bytes = sizeof( float ) * 4 * (size_t)( q1 - q0 );
+				CK( cudaMemcpyAsync( c->b.adam_m + o, c->peer_m[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
+				CK( cudaMemcpyAsync( c->b.adam_v + o, c->peer_v[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
+			}
+		}
+	}
 	int rc2 = ( splats || adam ) ? download_aos( c, image, splats, adam, nullptr ) : GS2D_OK;
 	if( rc2 )
 		return rc2;
@@ -733,6 +802,64 @@ static int enqueue_allreduce( gs2d_ctx* c )
 	return GS2D_OK;
 }
 
+// The exchange + update of one iteration (main.cpp:714-750 across ranks), after the backward pass.
+//   one GPU            : k_advance, k_adam
+//   NCCL path          : all-reduce of the 9 gradient planes and of the loss, then the same two kernels on every rank
+//   peer-memory path   : all-reduce of the loss only (it doubles as the "all gradients are final" barrier), then ONE
+//                        kernel that sums the peers' gradients for the slice this rank owns, runs Adam on it and stores
+//                        the new parameters into every rank's planes; a one-int all-reduce (the non-finite flag) is
+//                        the "all parameters have arrived" barrier; each rank then clears its own gradient planes.
+// ev_mid (optional) is recorded between the collective and the update (profiling groups 4 and 5).
+static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_reduced )
+{
+	cudaStream_t s = c->stream;
+	const bool dbg = c->comm && c->peer_update && gs2d_tune( "GS2D_PEER_DEBUG", 0 ) && c->dbg_ev.size() < 5 * 4096;
+	auto mark = [&]() {
+		if( dbg )
+		{
+			cudaEvent_t e;
+			cudaEventCreate( &e );
+			cudaEventRecord( e, s );
+			c->dbg_ev.push_back( e );
+		}
+	};
+	if( c->comm && c->peer_update )
+	{
+		mark();
+		int e = 0;
+		if( !grads_already_reduced ) // else gs2d_backward has reduced gradients and loss already
+			e = g_nccl.AllReduce( c->b.loss, c->b.loss, (size_t)c->g.n_images + 1, NCCL_FLOAT64, NCCL_SUM, c->comm, s );
+		if( e )
+			return nccl_fail( c, "ncclAllReduce(loss)", e );
+		if( ev_mid )
+			cudaEventRecord( ev_mid, s );
+		mark();
+		c->launches += launch_advance( c->g, c->b, c->hp, s );
+		PeerPtrs pp = c->peers;
+		pp.sum_all = grads_already_reduced ? 0 : 1;
+		c->launches += launch_adam_peer( c->g, c->b, c->hp, pp, c->own_q0, c->own_q1, s );
+		mark();
+		e = g_nccl.AllReduce( &c->b.state->nonfinite, &c->b.state->nonfinite, 1, NCCL_INT32, NCCL_MAX, c->comm, s );
+		if( e )
+			return nccl_fail( c, "ncclAllReduce(flag)", e );
+		mark();
+		CK( cudaMemsetAsync( c->b.grads, 0, sizeof( float ) * (size_t)c->g.n_pad * GS2D_NPLANES, s ) );
+		mark();
+		return GS2D_OK;
+	}
+	if( !grads_already_reduced )
+	{
+		int rc = enqueue_allreduce( c );
+		if( rc )
+			return rc;
+	}
+	if( ev_mid )
+		cudaEventRecord( ev_mid, s );
+	c->launches += launch_advance( c->g, c->b, c->hp, s );
+	c->launches += launch_adam( c->g, c->b, c->hp, s );
+	return GS2D_OK;
+}
+
 static int enqueue_iteration( gs2d_ctx* c )
 {
 	cudaStream_t s = c->stream;
@@ -762,12 +889,9 @@ static int enqueue_iteration( gs2d_ctx* c )
 	PROF( 3 );
 	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s );
 	PROF( 4 );
-	int rc = enqueue_allreduce( c );
+	int rc = enqueue_update( c, pr ? pr->ev[5] : nullptr, false );
 	if( rc )
 		return rc;
-	PROF( 5 );
-	c->launches += launch_advance( c->g, c->b, c->hp, s );
-	c->launches += launch_adam( c->g, c->b, c->hp, s );
 	PROF( 6 );
 #undef PROF
 	c->expected_iteration++;
@@ -920,8 +1044,9 @@ extern "C" int gs2d_adam( gs2d_ctx* c )
 	if( !c )
 		return GS2D_ERR_INVALID;
 	CK( cudaSetDevice( c->device ) );
-	c->launches += launch_advance( c->g, c->b, c->hp, c->stream );
-	c->launches += launch_adam( c->g, c->b, c->hp, c->stream );
+	int rcu = enqueue_update( c, nullptr, true ); // gs2d_backward has already summed gradients and loss over ranks
+	if( rcu )
+		return rcu;
 	c->expected_iteration++;
 	c->have_forward = false;
 	int rc = check_launch( c );
@@ -1107,6 +1232,104 @@ extern "C" int gs2d_comm_unique_id( uint8_t id[128] )
 	return GS2D_OK;
 }
 
+// Map the other ranks' gradient, parameter and Adam-moment planes into this process (CUDA IPC; NVLink peer access)
+// for the fused reduce + Adam + broadcast kernel. Collective: every rank calls it from gs2d_comm_init. If any rank
+// cannot map any peer (no P2P, IPC unavailable in this container, GS2D_PEER_ADAM=0) ALL ranks keep the NCCL path.
+static int setup_peer_update( gs2d_ctx* c )
+{
+	c->peer_update = false;
+	const int n = c->n_ranks;
+	if( n > GS2D_MAX_RANKS || !g_nccl.AllGather )
+		return GS2D_OK;
+	cudaStream_t s = c->stream;
+	struct Blob
+	{
+		cudaIpcMemHandle_t h[4];
+		int ok;
+		int pad[3];
+	};
+	Blob mine{};
+	float* local[4] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v };
+	mine.ok = gs2d_tune( "GS2D_PEER_ADAM", 1 ) ? 1 : 0;
+	for( int k = 0; k < 4 && mine.ok; k++ )
+		if( cudaIpcGetMemHandle( &mine.h[k], local[k] ) != cudaSuccess )
+			mine.ok = 0;
+	cudaGetLastError();
+	Blob* dev = nullptr;
+	CK( cudaMalloc( &dev, sizeof( Blob ) * ( (size_t)n + 1 ) ) );
+	CK( cudaMemcpyAsync( dev + n, &mine, sizeof( Blob ), cudaMemcpyHostToDevice, s ) );
+	int e = g_nccl.AllGather( dev + n, dev, sizeof( Blob ), NCCL_UINT8, c->comm, s );
+	std::vector<Blob> all( (size_t)n );
+	if( !e )
+	{
+		CK( cudaMemcpyAsync( all.data(), dev, sizeof( Blob ) * (size_t)n, cudaMemcpyDeviceToHost, s ) );
+		CK( cudaStreamSynchronize( s ) );
+	}
+	int ok = e ? 0 : 1;
+	for( int r = 0; r < n && ok; r++ )
+		ok = all[r].ok;
+	PeerPtrs pp{};
+	pp.n_ranks = n;
+	pp.rank = c->rank;
+	pp.sum_all = 1;
+	for( int r = 0; r < n && ok; r++ )
+	{
+		void* ptr[4] = { local[0], local[1], local[2], local[3] };
+		if( r != c->rank )
+			for( int k = 0; k < 4 && ok; k++ )
+			{
+				if( cudaIpcOpenMemHandle( &ptr[k], all[r].h[k], cudaIpcMemLazyEnablePeerAccess ) != cudaSuccess )
+				{
+					ok = 0;
+					cudaGetLastError();
+				}
+				else
+					c->ipc_opened.push_back( ptr[k] );
+			}
+		pp.grads[r] = (const float*)ptr[0];
+		pp.params[r] = (float*)ptr[1];
+		c->peer_m[r] = (float*)ptr[2];
+		c->peer_v[r] = (float*)ptr[3];
+	}
+	// agree: the peer path is used only if every rank mapped every peer
+	int* flag = reinterpret_cast<int*>( dev );
+	CK( cudaMemcpyAsync( flag, &ok, sizeof( int ), cudaMemcpyHostToDevice, s ) );
+	e = g_nccl.AllReduce( flag, flag, 1, NCCL_INT32, NCCL_MIN, c->comm, s );
+	int agreed = 0;
+	if( !e )
+	{
+		CK( cudaMemcpyAsync( &agreed, flag, sizeof( int ), cudaMemcpyDeviceToHost, s ) );
+		CK( cudaStreamSynchronize( s ) );
+	}
+	cudaFree( dev );
+	if( e )
+		return nccl_fail( c, "peer setup collective", e );
+	if( agreed )
+	{
+		c->peers = pp;
+		owned_quads( c, c->rank, &c->own_q0, &c->own_q1 );
+		c->peer_update = true;
+	}
+	else
+	{
+		for( void* p : c->ipc_opened )
+			cudaIpcCloseMemHandle( p );
+		c->ipc_opened.clear();
+	}
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_comm_mode( const gs2d_ctx* c, int* n_ranks, int* peer_memory )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	if( n_ranks )
+		*n_ranks = c->comm ? c->n_ranks : 1;
+	if( peer_memory )
+		*peer_memory = ( c->comm && c->peer_update ) ? 1 : 0;
+	return GS2D_OK;
+}
+
 extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t id[128] )
 {
 	if( !c || !id || n_ranks <= 0 || rank < 0 || rank >= n_ranks )
@@ -1132,5 +1355,5 @@ extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t
 		c->comm = nullptr;
 		return GS2D_ERR_NCCL;
 	}
-	return GS2D_OK;
+	return setup_peer_update( c );
 }

@@ -190,6 +190,20 @@ int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool w
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
 int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
+// Fused gradient reduction + Adam + parameter broadcast over peer memory (NVLink / NVSwitch, CUDA IPC mappings):
+// this rank owns the quads [q0, q1) of every plane; it sums the gradients of all ranks for them straight out of the
+// peers' HBM, runs Adam on them (its m, v are the only valid ones for that slice) and stores the new parameters into
+// every rank's parameter planes.
+#define GS2D_MAX_RANKS 16
+struct PeerPtrs
+{
+	const float* grads[GS2D_MAX_RANKS];
+	float* params[GS2D_MAX_RANKS];
+	int n_ranks, rank;
+	int sum_all; // 1: sum the gradients of all ranks; 0: this rank's gradients are already the total
+};
+int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p, const PeerPtrs& pp, int q0, int q1,
+                      cudaStream_t s );
 int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,
                        const gs2d_splat_adam* adam_dev, cudaStream_t s );
 int launch_soa_to_aos( const Geometry& g, const Buffers& b, int image, gs2d_splat* splats_dev,

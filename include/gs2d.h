@@ -152,6 +152,13 @@ int gs2d_get_stats( gs2d_ctx* ctx, gs2d_stats* out );                      /* co
  * and every rank calls gs2d_comm_init. One process per GPU. */
 int gs2d_comm_unique_id( uint8_t id[128] );
 int gs2d_comm_init( gs2d_ctx* ctx, int rank, int n_ranks, const uint8_t id[128] );
+/* How the ranks exchange gradients. peer_memory = 1: gs2d_comm_init mapped every peer's gradient / parameter / moment
+ * planes through CUDA IPC (NVLink peer access) and the exchange is ONE kernel per rank that sums the peers' gradients
+ * for the slice of Gaussians it owns, runs Adam on it and stores the new parameters into every rank's planes (the
+ * Adam moments are then sharded; gs2d_download_state gathers them). peer_memory = 0: NCCL all-reduce of the nine
+ * gradient planes followed by the identical Adam on every rank (chosen automatically when a peer cannot be mapped,
+ * or with the environment variable GS2D_PEER_ADAM=0). */
+int gs2d_comm_mode( const gs2d_ctx* ctx, int* n_ranks, int* peer_memory );
 /* Band sharding WITHOUT a communicator (host-side tests on one GPU: render bands separately and add them up). */
 int gs2d_set_band( gs2d_ctx* ctx, int rank, int n_ranks );
 

@@ -20,8 +20,9 @@ with gs2d.Fitter(W, H, N, device=local) as fit:
     fit.comm_init(rank, world, box[0])
     fit.set_target_u8(target)
     fit.restart()
+    mode = fit.comm_mode()
     mse_n = fit.step(ITERS)[:, 0]
-    s_n = fit.download()[0]
+    s_n, a_n, b1_n, b2_n, it_n = fit.download()
     img_n = fit.image()
 ok = True
 if rank == 0:
@@ -29,11 +30,19 @@ if rank == 0:
         fit.set_target_u8(target)
         fit.restart()
         mse_1 = fit.step(ITERS)[:, 0]
-        s_1 = fit.download()[0]
+        s_1, a_1, b1_1, b2_1, it_1 = fit.download()
     rel = np.abs(mse_n - mse_1) / mse_1
     d = np.abs(s_n.view(np.float32) - s_1.view(np.float32))
     print(f"world={world} mse rel diff max {rel.max():.3e}; params |diff| q99 {np.quantile(d, 0.99):.3e} max {d.max():.3e}")
-    ok = rel.max() < 1e-4 and np.quantile(d, 0.99) < 1e-2
+    # Adam moments: sharded over the ranks on the peer-memory path, gathered by download()
+    am, a1 = a_n.view(np.float32), a_1.view(np.float32)
+    da = np.abs(am - a1)
+    print(f"comm mode (n_ranks, peer_memory) = {mode}; adam |diff| q99 {np.quantile(da, 0.99):.3e} vs scale {np.abs(a1).mean():.3e}")
+    ok = rel.max() < 1e-4 and np.quantile(d, 0.99) < 1e-2 and (b1_n, b2_n, it_n) == (b1_1, b2_1, it_1)
+    ok = ok and np.quantile(da, 0.99) < 1e-3 * max(np.abs(a1).max(), 1e-30)
+    want_peer = os.environ.get("GS2D_PEER_ADAM", "1") != "0"
+    if os.environ.get("GS2D_EXPECT_PEER"):
+        ok = ok and mode[1] == want_peer
 # every rank must hold the same parameters after the all-reduced Adam
 t = torch.from_numpy(s_n.view(np.float32).copy()).cuda()
 tmin, tmax = t.clone(), t.clone()
