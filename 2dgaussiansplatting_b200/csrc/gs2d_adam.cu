@@ -160,6 +160,88 @@ __device__ __forceinline__ float4 ld_sys4( const float* p )
 	return v;
 }
 
+// ---- flag barriers over the peers' mailboxes ---------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys( unsigned long long* p, unsigned long long v )
+{
+	asm volatile( "st.release.sys.global.u64 [%0], %1;" ::"l"( p ), "l"( v ) : "memory" );
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys( const unsigned long long* p )
+{
+	unsigned long long v;
+	asm volatile( "ld.acquire.sys.global.u64 %0, [%1];" : "=l"( v ) : "l"( p ) : "memory" );
+	return v;
+}
+// spin until rank r's sequence number has reached seq; gives up after ~4 s (a peer died / diverged) and reports it
+__device__ __forceinline__ void wait_seq( const unsigned long long* flag, unsigned long long seq, DevState* st )
+{
+	const long long t0 = clock64();
+	while( ld_acquire_sys( flag ) < seq )
+	{
+		if( clock64() - t0 > 8000000000ll )
+		{
+			st->peer_fault = 1;
+			break;
+		}
+		__nanosleep( 100 );
+	}
+}
+__device__ __forceinline__ double* mailbox_loss( unsigned char* mb, int r, int L )
+{
+	return reinterpret_cast<double*>( mb + sizeof( PeerMailbox ) ) + (size_t)r * L;
+}
+
+// Barrier 1: "my backward pass is complete" + all-reduce of the loss. Thread t ships loss[t] to every rank's mailbox,
+// thread r publishes the sequence number to rank r and waits for rank r's; then the partial sums are added in rank
+// order, so every rank computes the identical total.
+__global__ void __launch_bounds__( 256 ) k_peer_loss_exchange( Geometry g, PeerPtrs pp, double* __restrict__ loss,
+                                                               unsigned long long seq, DevState* st )
+{
+	const int L = g.n_images + 1, me = pp.rank, n = pp.n_ranks;
+	for( int t = threadIdx.x; t < L; t += 256 )
+	{
+		const double v = loss[t];
+		for( int r = 0; r < n; r++ )
+			*( (volatile double*)mailbox_loss( pp.mbox[r], me, L ) + t ) = v;
+	}
+	__threadfence_system();
+	__syncthreads();
+	if( threadIdx.x < n )
+	{
+		PeerMailbox* theirs = reinterpret_cast<PeerMailbox*>( pp.mbox[threadIdx.x] );
+		st_release_sys( &theirs->seq1[me], seq );
+		const PeerMailbox* mine = reinterpret_cast<const PeerMailbox*>( pp.mbox[me] );
+		wait_seq( &mine->seq1[threadIdx.x], seq, st );
+	}
+	__syncthreads();
+	for( int t = threadIdx.x; t < L; t += 256 )
+	{
+		double sum = 0.0;
+		for( int r = 0; r < n; r++ )
+			sum += *( (volatile double*)mailbox_loss( pp.mbox[me], r, L ) + t );
+		loss[t] = sum;
+	}
+}
+
+// Barrier 2: "my stores into your parameter planes are complete" + OR of the non-finite flags.
+__global__ void __launch_bounds__( 32 ) k_peer_barrier2( PeerPtrs pp, unsigned long long seq, DevState* st )
+{
+	const int me = pp.rank, n = pp.n_ranks, r = threadIdx.x;
+	int any = 0;
+	if( r < n )
+	{
+		PeerMailbox* theirs = reinterpret_cast<PeerMailbox*>( pp.mbox[r] );
+		*( (volatile int*)&theirs->nf[me] ) = st->nonfinite;
+		__threadfence_system();
+		st_release_sys( &theirs->seq2[me], seq );
+		const PeerMailbox* mine = reinterpret_cast<const PeerMailbox*>( pp.mbox[me] );
+		wait_seq( &mine->seq2[r], seq, st );
+		any = *( (volatile const int*)&mine->nf[r] );
+	}
+	any = __any_sync( 0xffffffffu, any != 0 );
+	if( r == 0 && any )
+		st->nonfinite = 1;
+}
+
 // Reduce-scatter + Adam + all-gather in ONE kernel (the exchange step of the band-sharded fit): one
 // thread per (plane, quad) of the slice this rank owns (blockIdx.y = plane: the planes are independent scalars, and
 // nine times more threads keep nine times more NVLink loads in flight). NR = number of ranks (compile time, so that
@@ -249,8 +331,9 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	}
 	if( bad )
 		atomicOr( &st->nonfinite, 1 );
-	// the stores into the peers' planes are ordered before whatever this rank publishes next (the flag all-reduce)
-	asm volatile( "fence.acq_rel.sys;" ::: "memory" );
+	// No fence here (a system-scope fence per thread costs a third of the kernel): the stores into the peers' planes
+	// are complete when the grid is, and the barrier kernel that follows on the stream issues a cumulative
+	// __threadfence_system() before it publishes this rank's sequence number.
 }
 
 // ------------------------------------------------------------------------------------------------------ init ---
@@ -402,11 +485,21 @@ int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p,
 	switch( pp.n_ranks )
 	{
 		PEER_CASE( 2 ) PEER_CASE( 3 ) PEER_CASE( 4 ) PEER_CASE( 5 ) PEER_CASE( 6 ) PEER_CASE( 7 ) PEER_CASE( 8 )
-		PEER_CASE( 9 ) PEER_CASE( 10 ) PEER_CASE( 11 ) PEER_CASE( 12 ) PEER_CASE( 13 ) PEER_CASE( 14 ) PEER_CASE( 15 )
-		PEER_CASE( 16 )
 	default: return 0;
 	}
 #undef PEER_CASE
+	return 1;
+}
+int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+                               cudaStream_t s )
+{
+	k_peer_loss_exchange<<<1, 256, 0, s>>>( g, pp, b.loss, seq, b.state );
+	return 1;
+}
+int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+                          cudaStream_t s )
+{
+	k_peer_barrier2<<<1, 32, 0, s>>>( pp, seq, b.state );
 	return 1;
 }
 int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,

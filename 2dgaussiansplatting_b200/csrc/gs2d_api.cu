@@ -137,6 +137,9 @@ struct gs2d_ctx
 	float* peer_v[GS2D_MAX_RANKS] = {};
 	std::vector<void*> ipc_opened;
 	int own_q0 = 0, own_q1 = 0;
+	unsigned char* mbox = nullptr;          // this rank's mailbox (PeerMailbox), mapped by every peer
+	unsigned long long seq1 = 0, seq2 = 0;  // barrier sequence numbers (identical call sequence on every rank)
+	bool peer_flags = true;                 // barriers over the mailboxes (else tiny NCCL all-reduces): GS2D_PEER_FLAGS
 	// developer timing of the pieces of the peer-memory update (GS2D_PEER_DEBUG=1): events around barrier 1, the
 	// fused kernel, barrier 2 and the gradient clear of every iteration; averages are printed by gs2d_destroy
 	std::vector<cudaEvent_t> dbg_ev;
@@ -313,7 +316,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage };
+	                 b.state,      c->dstage, c->mbox };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -828,7 +831,12 @@ static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_r
 		mark();
 		int e = 0;
 		if( !grads_already_reduced ) // else gs2d_backward has reduced gradients and loss already
-			e = g_nccl.AllReduce( c->b.loss, c->b.loss, (size_t)c->g.n_images + 1, NCCL_FLOAT64, NCCL_SUM, c->comm, s );
+		{
+			if( c->peer_flags )
+				c->launches += launch_peer_loss_exchange( c->g, c->b, c->peers, ++c->seq1, s );
+			else
+				e = g_nccl.AllReduce( c->b.loss, c->b.loss, (size_t)c->g.n_images + 1, NCCL_FLOAT64, NCCL_SUM, c->comm, s );
+		}
 		if( e )
 			return nccl_fail( c, "ncclAllReduce(loss)", e );
 		if( ev_mid )
@@ -839,7 +847,10 @@ static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_r
 		pp.sum_all = grads_already_reduced ? 0 : 1;
 		c->launches += launch_adam_peer( c->g, c->b, c->hp, pp, c->own_q0, c->own_q1, s );
 		mark();
-		e = g_nccl.AllReduce( &c->b.state->nonfinite, &c->b.state->nonfinite, 1, NCCL_INT32, NCCL_MAX, c->comm, s );
+		if( c->peer_flags )
+			c->launches += launch_peer_barrier2( c->g, c->b, c->peers, ++c->seq2, s );
+		else
+			e = g_nccl.AllReduce( &c->b.state->nonfinite, &c->b.state->nonfinite, 1, NCCL_INT32, NCCL_MAX, c->comm, s );
 		if( e )
 			return nccl_fail( c, "ncclAllReduce(flag)", e );
 		mark();
@@ -927,6 +938,11 @@ static int resolve( gs2d_ctx* c )
 		if( rc )
 			return rc;
 		const DevState& s = *c->h_state;
+		if( s.peer_fault )
+		{
+			snprintf( c->err, sizeof( c->err ), "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
+			return GS2D_ERR_NCCL;
+		}
 		const long long missing = c->expected_iteration - (long long)s.iteration;
 		if( s.need_capacity == 0 && missing <= 0 )
 		{
@@ -1244,14 +1260,20 @@ static int setup_peer_update( gs2d_ctx* c )
 	cudaStream_t s = c->stream;
 	struct Blob
 	{
-		cudaIpcMemHandle_t h[4];
+		cudaIpcMemHandle_t h[5];
 		int ok;
 		int pad[3];
 	};
 	Blob mine{};
-	float* local[4] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v };
+	if( !c->mbox )
+	{
+		CK( cudaMalloc( &c->mbox, peer_mailbox_bytes( c->g.n_images ) ) );
+		CK( cudaMemset( c->mbox, 0, peer_mailbox_bytes( c->g.n_images ) ) );
+	}
+	void* local[5] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v, c->mbox };
 	mine.ok = gs2d_tune( "GS2D_PEER_ADAM", 1 ) ? 1 : 0;
-	for( int k = 0; k < 4 && mine.ok; k++ )
+	c->peer_flags = gs2d_tune( "GS2D_PEER_FLAGS", 1 ) != 0;
+	for( int k = 0; k < 5 && mine.ok; k++ )
 		if( cudaIpcGetMemHandle( &mine.h[k], local[k] ) != cudaSuccess )
 			mine.ok = 0;
 	cudaGetLastError();
@@ -1274,9 +1296,9 @@ static int setup_peer_update( gs2d_ctx* c )
 	pp.sum_all = 1;
 	for( int r = 0; r < n && ok; r++ )
 	{
-		void* ptr[4] = { local[0], local[1], local[2], local[3] };
+		void* ptr[5] = { local[0], local[1], local[2], local[3], local[4] };
 		if( r != c->rank )
-			for( int k = 0; k < 4 && ok; k++ )
+			for( int k = 0; k < 5 && ok; k++ )
 			{
 				if( cudaIpcOpenMemHandle( &ptr[k], all[r].h[k], cudaIpcMemLazyEnablePeerAccess ) != cudaSuccess )
 				{
@@ -1290,6 +1312,7 @@ static int setup_peer_update( gs2d_ctx* c )
 		pp.params[r] = (float*)ptr[1];
 		c->peer_m[r] = (float*)ptr[2];
 		c->peer_v[r] = (float*)ptr[3];
+		pp.mbox[r] = (unsigned char*)ptr[4];
 	}
 	// agree: the peer path is used only if every rank mapped every peer
 	int* flag = reinterpret_cast<int*>( dev );

@@ -58,7 +58,7 @@ struct DevState
 	unsigned long long n_keys; // total list entries of the current iteration (written by the scan)
 	unsigned long long need_capacity; // != 0: the key buffers were too small; the iteration was skipped
 	int mse_slot;              // next slot of the mse ring written by k_finalize
-	int pad;
+	int peer_fault;            // a peer-memory barrier timed out (a rank died or the call sequences diverged)
 };
 
 struct Geometry
@@ -194,14 +194,37 @@ int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cuda
 // this rank owns the quads [q0, q1) of every plane; it sums the gradients of all ranks for them straight out of the
 // peers' HBM, runs Adam on them (its m, v are the only valid ones for that slice) and stores the new parameters into
 // every rank's parameter planes.
-#define GS2D_MAX_RANKS 16
+#define GS2D_MAX_RANKS 8
 struct PeerPtrs
 {
 	const float* grads[GS2D_MAX_RANKS];
 	float* params[GS2D_MAX_RANKS];
 	int n_ranks, rank;
 	int sum_all; // 1: sum the gradients of all ranks; 0: this rank's gradients are already the total
+	// mailboxes for the flag barriers (one per rank, mapped everywhere): see PeerMailbox
+	unsigned char* mbox[GS2D_MAX_RANKS];
 };
+// Layout of a rank's mailbox; slot r of every array is written only by rank r (so no atomics are needed):
+//   seq1[r], seq2[r]  : sequence numbers of the last barrier-1 / barrier-2 rank r has arrived at (release stores)
+//   nf[r]             : rank r's non-finite flag, payload of barrier 2
+//   loss[r][0..L)     : rank r's band sums of the loss + its overflow vote, payload of barrier 1 (L = n_images + 1)
+struct PeerMailbox
+{
+	unsigned long long seq1[GS2D_MAX_RANKS];
+	unsigned long long seq2[GS2D_MAX_RANKS];
+	int nf[GS2D_MAX_RANKS];
+	// double loss[GS2D_MAX_RANKS][L] follows
+};
+static inline size_t peer_mailbox_bytes( int n_images )
+{
+	return sizeof( PeerMailbox ) + sizeof( double ) * GS2D_MAX_RANKS * ( (size_t)n_images + 1 );
+}
+// Barrier 1 + all-reduce of the loss over the mailboxes (replaces ncclAllReduce of n_images + 1 doubles), and
+// barrier 2 + OR of the non-finite flags. One small block each; seq must increase by one per call on every rank.
+int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+                               cudaStream_t s );
+int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+                          cudaStream_t s );
 int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p, const PeerPtrs& pp, int q0, int q1,
                       cudaStream_t s );
 int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,
