@@ -355,7 +355,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	if( !out )
 		return GS2D_ERR_INVALID;
 	*out = nullptr;
-	if( W <= 0 || H <= 0 || n_splats < 0 || n_images <= 0 || W > 65535 * GS2D_TILE || H > 65535 * GS2D_TILE )
+	if( W <= 0 || H <= 0 || n_splats < 0 || n_images <= 0 || W > 4096 * GS2D_TILE || H > 65535 * GS2D_TILE ) // tile columns are 12-bit fields in k_preprocess
 		return GS2D_ERR_INVALID;
 	if( (long long)n_splats * n_images > 0x7FFF0000ll || n_images > 65535 )
 		return GS2D_ERR_INVALID;

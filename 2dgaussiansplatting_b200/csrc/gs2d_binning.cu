@@ -8,6 +8,7 @@
 //   bucket = (tile, index slice): the splat indices of an image are cut into n_slices equal slices (<= 65535 splats
 //   each), so a bucket holds the few splats of one slice that touch one tile (3.3 on average at 4096^2 / 1 M).
 //   k_preprocess   : covariance, inverse, row range (cov_of main.cpp:206-221, :432-436, :489-491) -> 64-byte record;
+//                    then, warp-cooperatively over (splat, tile row) work items:
 //                    the tiles the 3-sigma ellipse can touch (per tile row: the x-extent of the ellipse inside the
 //                    band of that row's pixel centres, see tile_span) are emitted as unordered (bucket, splat, rank)
 //                    triples packed into one 64-bit word, rank = arrival order in the bucket. The bucket counters are 16 bits wide and the
@@ -78,7 +79,7 @@ struct SplatBin
 	int local;     // index of the splat inside its slice
 };
 
-#define BIG_RECT 1024 // rectangles with more tiles than this are binned by the whole warp
+#define ITEMS_PER_CHUNK 256 // (splat, tile row) work items a warp handles per reservation of the pair list
 
 // One emitted (tile, splat) pair is ONE 64-bit word: bucket = tile * n_slices + slice in the low half, then the
 // splat's index inside its slice (16 bits; slice_size <= 65535) and the arrival order inside the bucket (16 bits).
@@ -218,88 +219,93 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		sb.k.endY = endY;
 	}
 	const bool has = sb.ty0 <= sb.ty1 && sb.rtx0 <= sb.rtx1;
-	const bool big = has && (long long)( sb.ty1 - sb.ty0 + 1 ) * ( sb.rtx1 - sb.rtx0 + 1 ) > BIG_RECT;
 
-	// phase A: number of pairs of this splat (small rectangles only)
-	unsigned cnt = 0;
-	if( has && !big )
-		for( int ty = sb.ty0; ty <= sb.ty1; ty++ )
-		{
-			int lo, hi;
-			if( tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
-				cnt += (unsigned)( hi - lo + 1 );
-		}
-
-	// block-exclusive scan of cnt, one reservation in the pair list per block
-	__shared__ unsigned warp_tot[PRE_THREADS / 32];
-	__shared__ unsigned long long block_base;
-	unsigned incl = cnt;
+	// ---- emission, warp-cooperative -----------------------------------------------------------------------------
+	// A work item is one (splat, tile row). The items of the warp's 32 splats are numbered consecutively and dealt to
+	// the lanes 32 at a time, so a warp whose splats have 1, 9 or no rows at all (a rank whose band most splats miss)
+	// still runs with full lanes, and a splat at the 1024 clamp (hundreds of tile rows) is shared by the whole warp.
+	// Items are handled in chunks of ITEMS_PER_CHUNK: spans first (stashed in shared memory), ONE reservation of the
+	// pair list per chunk, then the emission.
+	__shared__ SplatBin s_bin[PRE_THREADS];
+	__shared__ unsigned s_rows[PRE_THREADS];          // inclusive scan of the row counts inside the warp
+	__shared__ unsigned s_span[PRE_THREADS / 32][ITEMS_PER_CHUNK]; // lo | hi << 12 | owner lane << 24, ~0 = no tile
+	SplatBin* wbin = s_bin + warp * 32;
+	unsigned* wrows = s_rows + warp * 32;
+	unsigned* wspan = s_span[warp];
+	wbin[lane] = sb;
+	unsigned rows_incl = has ? (unsigned)( sb.ty1 - sb.ty0 + 1 ) : 0u;
 #pragma unroll
 	for( int o = 1; o < 32; o <<= 1 )
 	{
-		unsigned v = __shfl_up_sync( 0xffffffffu, incl, o );
+		const unsigned v = __shfl_up_sync( 0xffffffffu, rows_incl, o );
 		if( lane >= o )
-			incl += v;
+			rows_incl += v;
 	}
-	if( lane == 31 )
-		warp_tot[warp] = incl;
-	__syncthreads();
-	unsigned wbase = 0, total = 0;
-#pragma unroll
-	for( int w = 0; w < PRE_THREADS / 32; w++ )
-	{
-		unsigned t = warp_tot[w];
-		if( w < warp )
-			wbase += t;
-		total += t;
-	}
-	if( threadIdx.x == 0 )
-		block_base = total ? atomicAdd( &st->n_keys, (unsigned long long)total ) : 0ull;
-	__syncthreads();
+	wrows[lane] = rows_incl;
+	const unsigned R = __shfl_sync( 0xffffffffu, rows_incl, 31 );
+	__syncwarp();
 
-	// phase B: emit the pairs
-	if( cnt && block_base + total <= capacity )
+	for( unsigned chunk = 0; chunk < R; chunk += ITEMS_PER_CHUNK )
 	{
-		unsigned long long pos = block_base + wbase + incl - cnt;
-		for( int ty = sb.ty0; ty <= sb.ty1; ty++ )
+		const unsigned n_items = min( (unsigned)ITEMS_PER_CHUNK, R - chunk );
+		// pass A: spans of the chunk's items
+		unsigned cnt = 0;
+		for( unsigned it = lane; it < n_items; it += 32 )
 		{
-			int lo, hi;
-			if( !tile_span( sb.k, ty, g.H, sb.rtx0, sb.rtx1, lo, hi ) )
-				continue;
-			const unsigned row = (unsigned)( sb.tile_base + ty * g.tiles_x );
-			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, sb.slice, (unsigned)sb.local, pos );
-			pos += (unsigned)( hi - lo + 1 );
-		}
-	}
-
-	// phase C: big rectangles, one splat at a time by the whole warp: lanes take tile rows, each row reserves its own
-	// run of the pair list
-	unsigned bigs = __ballot_sync( 0xffffffffu, big );
-	while( bigs )
-	{
-		const int j = __ffs( bigs ) - 1;
-		bigs &= bigs - 1u;
-		SplatBin o;
-		{
-			const int* srcw = reinterpret_cast<const int*>( &sb );
-			int* dstw = reinterpret_cast<int*>( &o );
+			const unsigned item = chunk + it;
+			// owner = first lane whose inclusive row count exceeds the item number (binary search, 5 steps)
+			unsigned owner = 0;
 #pragma unroll
-			for( int w = 0; w < (int)( sizeof( SplatBin ) / 4 ); w++ )
-				dstw[w] = __shfl_sync( 0xffffffffu, srcw[w], j );
-		}
-		const int gj = gi - lane + j;
-		for( int ty = o.ty0 + lane; ty <= o.ty1; ty += 32 )
-		{
+			for( int step = 16; step > 0; step >>= 1 )
+				if( wrows[owner + step - 1] <= item )
+					owner += step;
+			const SplatBin& o = wbin[owner];
+			const unsigned first = owner ? wrows[owner - 1] : 0u;
+			const int ty = o.ty0 + (int)( item - first );
 			int lo, hi;
-			if( !tile_span( o.k, ty, g.H, o.rtx0, o.rtx1, lo, hi ) )
-				continue;
-			const unsigned n = (unsigned)( hi - lo + 1 );
-			const unsigned long long pos = atomicAdd( &st->n_keys, (unsigned long long)n );
-			if( pos + n > capacity )
-				continue;
-			const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-			emit_row( g, out, row + (unsigned)lo, row + (unsigned)hi, o.slice, (unsigned)o.local, pos );
+			unsigned span = 0xffffffffu;
+			if( tile_span( o.k, ty, g.H, o.rtx0, o.rtx1, lo, hi ) )
+			{
+				span = (unsigned)lo | ( (unsigned)hi << 12 ) | ( owner << 24 ); // tiles_x <= 4096 (gs2d_create)
+				cnt += (unsigned)( hi - lo + 1 );
+			}
+			wspan[it] = span;
 		}
+		// one reservation per chunk
+		unsigned incl = cnt;
+#pragma unroll
+		for( int o = 1; o < 32; o <<= 1 )
+		{
+			const unsigned v = __shfl_up_sync( 0xffffffffu, incl, o );
+			if( lane >= o )
+				incl += v;
+		}
+		const unsigned total = __shfl_sync( 0xffffffffu, incl, 31 );
+		unsigned long long base = 0;
+		if( lane == 0 && total )
+			base = atomicAdd( &st->n_keys, (unsigned long long)total );
+		base = __shfl_sync( 0xffffffffu, base, 0 );
+		__syncwarp();
+		// pass B: emit (skipped when the list is full: the scan flags the overflow and the host redoes the iteration)
+		if( total && base + total <= capacity )
+		{
+			unsigned long long pos = base + incl - cnt;
+			for( unsigned it = lane; it < n_items; it += 32 )
+			{
+				const unsigned span = wspan[it];
+				if( span == 0xffffffffu )
+					continue;
+				const unsigned item = chunk + it, owner = span >> 24;
+				const SplatBin& o = wbin[owner];
+				const unsigned first = owner ? wrows[owner - 1] : 0u;
+				const int ty = o.ty0 + (int)( item - first );
+				const unsigned lo = span & 0xfffu, hi = ( span >> 12 ) & 0xfffu;
+				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
+				emit_row( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos );
+				pos += hi - lo + 1u;
+			}
+		}
+		__syncwarp();
 	}
 }
 
