@@ -88,8 +88,9 @@ __device__ __forceinline__ float adam_one( float value, float gr, float& m_io, f
 	return xsub( value, xdiv( xmul( lr, m_hat ), xadd( xsqrt( v_hat ), eps ) ) );
 }
 
-// One thread per 4 consecutive splats, 128-bit accesses on every SoA plane: reads p, g, m, v, writes p, m, v and
-// zeroes g for the next iteration (28 + 4 bytes per scalar; HBM-bound).
+// One thread per (plane, 4 consecutive splats) - blockIdx.y is the plane, the nine scalars of a splat are independent
+// in Adam (main.cpp:723-738) - 128-bit accesses on every SoA plane: reads p, g, m, v, writes p, m, v and zeroes g for the
+// next iteration (28 + 4 bytes per scalar; HBM-bound).
 __global__ void __launch_bounds__( 256 ) k_adam( Geometry g, float* __restrict__ params, float* __restrict__ grads,
                                                  float* __restrict__ adam_m, float* __restrict__ adam_v,
                                                  gs2d_params hp, const double* __restrict__ loss, DevState* st )
@@ -99,51 +100,48 @@ __global__ void __launch_bounds__( 256 ) k_adam( Geometry g, float* __restrict__
 	const int i4 = ( blockIdx.x * 256 + threadIdx.x ) * 4;
 	if( i4 >= g.n_total )
 		return;
-	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
-	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
-	bool bad = false;
-	// update order of the reference: colour, pos, sx, sy, rot, opacity (main.cpp:723-738) — independent scalars
-#pragma unroll
-	for( int pl = 0; pl < GS2D_NPLANES; pl++ )
+	const int pl = blockIdx.y;
+	const size_t o = (size_t)pl * g.n_pad + i4;
+	const bool optimised = pl != PL_OP || hp.optimize_opacity;
+	const float4 p = __ldcs( reinterpret_cast<const float4*>( params + o ) );
+	float pv[4] = { p.x, p.y, p.z, p.w };
+	if( optimised )
 	{
-		const size_t o = (size_t)pl * g.n_pad + i4;
-		float4 p = *reinterpret_cast<float4*>( params + o );
-		float4 gr = *reinterpret_cast<float4*>( grads + o );
-		float pv[4] = { p.x, p.y, p.z, p.w }, gv[4] = { gr.x, gr.y, gr.z, gr.w };
-		if( pl != PL_OP || hp.optimize_opacity )
-		{
-			float4 m = *reinterpret_cast<float4*>( adam_m + o );
-			float4 v = *reinterpret_cast<float4*>( adam_v + o );
-			float mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
-#pragma unroll
-			for( int k = 0; k < 4; k++ )
-				pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
-			*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
-			*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
-		}
-		// constraints, main.cpp:740-749
+		const float4 gr = __ldcs( reinterpret_cast<const float4*>( grads + o ) );
+		const float4 m = __ldcs( reinterpret_cast<const float4*>( adam_m + o ) );
+		const float4 v = __ldcs( reinterpret_cast<const float4*>( adam_v + o ) );
+		const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
+		float gv[4] = { gr.x, gr.y, gr.z, gr.w }, mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
 #pragma unroll
 		for( int k = 0; k < 4; k++ )
-		{
-			float x = pv[k];
-			if( pl == PL_PX )
-				x = clamp_glm( x, 0.0f, wmax );
-			else if( pl == PL_PY )
-				x = clamp_glm( x, 0.0f, hmax );
-			else if( pl == PL_SX || pl == PL_SY )
-				x = clamp_glm( x, hp.s_min, hp.s_max );
-			else if( pl == PL_CR || pl == PL_CG || pl == PL_CB )
-				x = clamp_glm( x, 0.0f, 1.0f );
-			else if( pl == PL_OP )
-				x = clamp_glm( x, hp.o_min, hp.o_max );
-			pv[k] = x;
-			// finite check, main.cpp:752-785: colour, sx, sy, rot, pos.x (pos.y and opacity are not checked)
-			if( pl != PL_PY && pl != PL_OP && i4 + k < g.n_total && !isfinite( x ) )
-				bad = true;
-		}
-		*reinterpret_cast<float4*>( params + o ) = make_float4( pv[0], pv[1], pv[2], pv[3] );
-		*reinterpret_cast<float4*>( grads + o ) = make_float4( 0.f, 0.f, 0.f, 0.f );
+			pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
+		*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
+		*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
 	}
+	// constraints, main.cpp:740-749 (the opacity clamp applies even when opacity is not optimised)
+	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
+	bool bad = false;
+#pragma unroll
+	for( int k = 0; k < 4; k++ )
+	{
+		float x = pv[k];
+		if( pl == PL_PX )
+			x = clamp_glm( x, 0.0f, wmax );
+		else if( pl == PL_PY )
+			x = clamp_glm( x, 0.0f, hmax );
+		else if( pl == PL_SX || pl == PL_SY )
+			x = clamp_glm( x, hp.s_min, hp.s_max );
+		else if( pl == PL_CR || pl == PL_CG || pl == PL_CB )
+			x = clamp_glm( x, 0.0f, 1.0f );
+		else if( pl == PL_OP )
+			x = clamp_glm( x, hp.o_min, hp.o_max );
+		pv[k] = x;
+		// finite check, main.cpp:752-785: colour, sx, sy, rot, pos.x (pos.y and opacity are not checked)
+		if( pl != PL_PY && pl != PL_OP && i4 + k < g.n_total && !isfinite( x ) )
+			bad = true;
+	}
+	*reinterpret_cast<float4*>( params + o ) = make_float4( pv[0], pv[1], pv[2], pv[3] );
+	*reinterpret_cast<float4*>( grads + o ) = make_float4( 0.f, 0.f, 0.f, 0.f );
 	if( bad )
 		atomicOr( &st->nonfinite, 1 );
 }
@@ -471,7 +469,8 @@ int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cuda
 	if( g.n_total == 0 )
 		return 0;
 	const int n4 = ( g.n_total + 3 ) / 4;
-	k_adam<<<( n4 + 255 ) / 256, 256, 0, s>>>( g, b.params, b.grads, b.adam_m, b.adam_v, p, b.loss, b.state );
+	k_adam<<<dim3( ( n4 + 255 ) / 256, GS2D_NPLANES ), 256, 0, s>>>( g, b.params, b.grads, b.adam_m, b.adam_v, p, b.loss,
+	                                                                 b.state );
 	return 1;
 }
 int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p, const PeerPtrs& pp, int q0, int q1,
