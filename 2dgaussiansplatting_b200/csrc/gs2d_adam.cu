@@ -11,22 +11,32 @@ __device__ __forceinline__ float clamp_glm( float x, float lo, float hi )
 
 // ------------------------------------------------------------------------------------------------------ loss ---
 // One block per image: deterministic sum of the per-tile partials of this rank's band (double).
-__global__ void __launch_bounds__( 256 ) k_finalize_loss( Geometry g, const double* __restrict__ loss_partial,
+#define LOSS_THREADS 1024
+__global__ void __launch_bounds__( LOSS_THREADS ) k_finalize_loss( Geometry g, const double* __restrict__ loss_partial,
                                                           double* __restrict__ loss,
                                                           const unsigned long long* __restrict__ slots,
                                                           unsigned long long* __restrict__ stats,
                                                           const DevState* __restrict__ st )
 {
-	__shared__ double red[256];
+	__shared__ double red[LOSS_THREADS];
 	const int img = blockIdx.x;
 	const int t0 = ( img * g.tiles_y + g.band_ty0 ) * g.tiles_x;
 	const int t1 = ( img * g.tiles_y + g.band_ty1 ) * g.tiles_x;
-	double s = 0.0;
-	for( int t = t0 + threadIdx.x; t < t1; t += 256 )
-		s += loss_partial[t];
-	red[threadIdx.x] = s;
+	// four independent partial sums per thread (loads in flight), combined in a fixed order: deterministic
+	double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+	int t = t0 + threadIdx.x;
+	for( ; t + 3 * LOSS_THREADS < t1; t += 4 * LOSS_THREADS )
+	{
+		s0 += loss_partial[t];
+		s1 += loss_partial[t + LOSS_THREADS];
+		s2 += loss_partial[t + 2 * LOSS_THREADS];
+		s3 += loss_partial[t + 3 * LOSS_THREADS];
+	}
+	for( ; t < t1; t += LOSS_THREADS )
+		s0 += loss_partial[t];
+	red[threadIdx.x] = ( s0 + s1 ) + ( s2 + s3 );
 	__syncthreads();
-	for( int o = 128; o > 0; o >>= 1 )
+	for( int o = LOSS_THREADS / 2; o > 0; o >>= 1 )
 	{
 		if( threadIdx.x < o )
 			red[threadIdx.x] += red[threadIdx.x + o];
@@ -456,7 +466,7 @@ int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaS
 }
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s )
 {
-	k_finalize_loss<<<g.n_images, 256, 0, s>>>( g, b.loss_partial, b.loss, b.live_slots, b.stats, b.state );
+	k_finalize_loss<<<g.n_images, LOSS_THREADS, 0, s>>>( g, b.loss_partial, b.loss, b.live_slots, b.stats, b.state );
 	return 1;
 }
 int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s )

@@ -409,15 +409,12 @@ __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ su
 		__syncthreads();
 	}
 }
-__global__ void __launch_bounds__( SCAN_THREADS ) k_scan_add( unsigned* __restrict__ offset, unsigned base,
-                                                              unsigned n, const unsigned* __restrict__ sums )
+// The block-local offsets are not patched in a third pass: the consumers add the scanned block total themselves
+// (16 KB of sums, cache resident).
+__device__ __forceinline__ unsigned bucket_offset( const unsigned* __restrict__ offset,
+                                                   const unsigned* __restrict__ sums, unsigned bucket, unsigned base )
 {
-	const unsigned add = sums[blockIdx.x];
-	const unsigned i0 = base + blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
-#pragma unroll
-	for( int k = 0; k < 4; k++ )
-		if( i0 + k < n )
-			offset[i0 + k] += add;
+	return __ldg( offset + bucket ) + __ldg( sums + ( ( bucket - base ) / SCAN_PER_BLOCK ) );
 }
 
 // ------------------------------------------------------------------------------------------- place and order ---
@@ -429,8 +426,9 @@ __device__ __forceinline__ unsigned splat_of_triple( const Geometry& g, unsigned
 }
 
 __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned long long* __restrict__ triple,
-                                                  const unsigned* __restrict__ offset, unsigned* __restrict__ list,
-                                                  const DevState* __restrict__ st )
+                                                  const unsigned* __restrict__ offset,
+                                                  const unsigned* __restrict__ sums, unsigned base,
+                                                  unsigned* __restrict__ list, const DevState* __restrict__ st )
 {
 	if( st->need_capacity )
 		return;
@@ -448,7 +446,7 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
 			t[k] = __ldcs( triple + i + k * stride );
 #pragma unroll
 		for( int k = 0; k < 4; k++ )
-			of[k] = __ldg( offset + (unsigned)t[k] );
+			of[k] = bucket_offset( offset, sums, (unsigned)t[k], base );
 #pragma unroll
 		for( int k = 0; k < 4; k++ )
 			list[of[k] + (unsigned)( t[k] >> 48 )] =
@@ -457,7 +455,7 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
 	for( ; i < n; i += stride )
 	{
 		const unsigned long long t = triple[i];
-		list[offset[(unsigned)t] + (unsigned)( t >> 48 )] =
+		list[bucket_offset( offset, sums, (unsigned)t, base ) + (unsigned)( t >> 48 )] =
 		    splat_of_triple( g, (unsigned)t, (unsigned)( t >> 32 ) & 0xffffu, tpi );
 	}
 }
@@ -465,6 +463,7 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
 // One thread per bucket: order its entries by splat index (rank by counting: the indices are unique), list -> out.
 __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned short* __restrict__ cnt16,
                                                  const unsigned* __restrict__ offset,
+                                                 const unsigned* __restrict__ sums,
                                                  const unsigned* __restrict__ list, unsigned* __restrict__ out,
                                                  uint2* __restrict__ tile_range, unsigned base, unsigned n_buckets,
                                                  const DevState* __restrict__ st )
@@ -476,7 +475,7 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		return;
 	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
 	const unsigned n = cnt16[(size_t)slice * g.nt_pad + tile];
-	const unsigned start = offset[i];
+	const unsigned start = bucket_offset( offset, sums, i, base );
 	if( slice == 0 )
 		tile_range[tile].x = start;
 	if( slice == (unsigned)g.n_slices - 1 )
@@ -557,10 +556,9 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
 	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, lo, hi, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
-	k_scan_add<<<scan_nb, SCAN_THREADS, 0, s>>>( b.bucket_off, lo, hi, b.scan_sums );
-	k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.vals[1], b.state );
-	k_rank<<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.vals[1], b.vals[0], b.tile_range, lo,
-	                                               hi, b.state );
-	launches += 5;
+	k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state );
+	k_rank<<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1], b.vals[0],
+	                                               b.tile_range, lo, hi, b.state );
+	launches += 4;
 	return launches;
 }

@@ -10,6 +10,7 @@ tail -5 $OUT/${TAG}_pytest.log
 timeout 600 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench exit $?"
 cat $OUT/${TAG}_bench.json | cut -c1-600
 if [ "$2" != "noncu" ]; then
+export GS2D_STATS=0   # profile the variant the timed run uses (work counters off)
 timeout 300 python tools/quick_time.py 4096 1000000 3 > $OUT/${TAG}_quick.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv \
     python tools/quick_time.py 4096 1000000 3 > $OUT/${TAG}_ncu1.log 2>&1
