@@ -88,8 +88,14 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	const int px_x = tile_x0 + ( lane & 7 ), px_y = tile_y0 + ( lane >> 3 );
 	const float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
 	const float fpy0 = (float)px_y + 0.5f;
+	// row coordinates and lane bit kept in registers (see k_forward)
+	float fpyr[4] = { fpy0, fpy0 + 4.0f, fpy0 + 8.0f, fpy0 + 12.0f };
+#pragma unroll
+	for( int r = 0; r < 4; r++ )
+		asm volatile( "" : "+f"( fpyr[r] ) );
 	const float min_T = g.min_throughput;
-	const unsigned lanebit = 1u << lane;
+	unsigned lanebit = 1u << lane;
+	asm volatile( "" : "+r"( lanebit ) );
 
 	const uint2 range = tile_range[tile_id];
 	const unsigned start = range.x, end = range.y;
@@ -190,14 +196,13 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				if( COUNT )
 					nlive += cov ? 1u : 0u;
 				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
-				const float vy = xsub( fpy0 + (float)( 4 * ( j >> 1 ) ), q0.y );
+				const float vy = xsub( fpyr[j >> 1], q0.y );
 				const float rx = xadd( avx, xmul( q0.w, vy ) );
 				const float ry = xadd( bvx, xmul( q1.x, vy ) );
 				const float d2 = xadd( xmul( vx, rx ), xmul( vy, ry ) );
 				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
 				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
-				const bool on = cov && !( t < 0.00001814586175896693021059036255f );
-				const float G = on ? t8 : 0.0f;              // main.cpp:610
+				const float G = select_alpha( wl & lanebit, t, t8 ); // main.cpp:610; 0 for uncovered / dead lanes
 				const float alpha = xmul( G, op );           // main.cpp:611 (0 for uncovered / dead lanes)
 				const float wgt = alpha * T[j];              // dC_dc, main.cpp:618
 				gc0 = fmaf( dLr[j], wgt, gc0 );
@@ -209,7 +214,10 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				const bool dead = Tn < min_T;
 				float Qn = fmaf( -alpha, D, Q[j] );
 				Qn = dead ? 0.0f : Qn;                       // nothing behind a dead pixel: the reference's S is exactly 0
-				const float inv = __fdividef( 1.0f, oma + 1.0e-15f ); // MUFU.RCP; main.cpp:628
+				// 1 / ( 1 - alpha + 1e-15 ), main.cpp:628: one MUFU.RCP (the argument is >= 1e-15, never subnormal, so
+				// the range fix-up __fdividef wraps around the instruction is not needed)
+				float inv;
+				asm( "rcp.approx.ftz.f32 %0, %1;" : "=f"( inv ) : "f"( oma + 1.0e-15f ) );
 				const float gsum = fmaf( -inv, Qn, D );      // dL_dalpha_rgb, main.cpp:629-630
 				const float ga = gsum * alpha;
 				const float gav = ga * vy;
@@ -322,7 +330,8 @@ int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool w
 	switch( gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT ) )
 	{
 	case 16: LAUNCH_BWD( 16 ); break;
-	default: LAUNCH_BWD( 20 ); break;
+	case 20: LAUNCH_BWD( 20 ); break;
+	default: LAUNCH_BWD( 24 ); break;
 	}
 #undef LAUNCH_BWD
 #undef LAUNCH_BWD3

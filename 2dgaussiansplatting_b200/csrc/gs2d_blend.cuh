@@ -14,6 +14,20 @@
 #pragma once
 #include "gs2d_internal.cuh"
 
+// ( covered != 0 && !( t < exp_approx's cut-off ) ) ? value : 0 in three instructions (LOP3 with predicate output,
+// FSETP.GEU.AND on that predicate, FSEL): main.cpp:60 (`t < 0.000018...` -> 0) and the footprint / liveness test.
+__device__ __forceinline__ float select_alpha( unsigned covered, float t, float value )
+{
+	float r;
+	asm( "{\n\t.reg .pred pc, pt;\n\t"
+	     "setp.ne.u32 pc, %1, 0;\n\t"
+	     "setp.geu.and.f32 pt, %2, 0f379837F1, pc;\n\t" // !( t < 1.8145861e-5f ); NaN -> true like the reference's `<`
+	     "selp.f32 %0, %3, 0f00000000, pt;\n\t}"
+	     : "=f"( r )
+	     : "r"( covered ), "f"( t ), "f"( value ) );
+	return r;
+}
+
 // WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)
 template <int WSTAGES>
 struct TileSmem

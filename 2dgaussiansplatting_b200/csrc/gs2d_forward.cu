@@ -16,6 +16,10 @@
 
 // MINB = resident warps (tiles) per SM the register allocation is capped for: 32 -> 64 registers, 24 -> 80, 20 -> 96.
 // COUNT: also count the live (pixel, splat) pairs (statistics for the roofline; one more instruction per block visit).
+// developer statistic (GS2D_VISIT_HIST=1, counting variant only): histogram of the number of covered-and-live lanes
+// per 8x4 block visit, and of the live pixels left in the tile at each visit
+__device__ unsigned long long g_visit_hist[2][33];
+
 template <int MINB, bool COUNT>
 __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const SplatRec* __restrict__ rec,
                                                              const unsigned* __restrict__ vals,
@@ -26,7 +30,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
                                                              double* __restrict__ loss_partial,
                                                              unsigned long long* __restrict__ live_slots,
                                                              unsigned long long* __restrict__ staged_slots,
-                                                             const DevState* __restrict__ st )
+                                                             const DevState* __restrict__ st, int visit_hist )
 {
 	if( st->need_capacity )
 		return;
@@ -40,8 +44,15 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 	// glm::vec2 p = { x + 0.5f, y + 0.5f }, main.cpp:523 (small integers + 0.5 are exact, so is adding 4 or 8)
 	const float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
 	const float fpy0 = (float)px_y + 0.5f;
+	// the four row coordinates of a lane, kept in registers (opaque to the compiler, which would otherwise rebuild
+	// them from the integer at every block visit: I2FP + 2 FADD)
+	float fpyr[4] = { fpy0, fpy0 + 4.0f, fpy0 + 8.0f, fpy0 + 12.0f };
+#pragma unroll
+	for( int r = 0; r < 4; r++ )
+		asm volatile( "" : "+f"( fpyr[r] ) );
 	const float min_T = g.min_throughput;
-	const unsigned lanebit = 1u << lane;
+	unsigned lanebit = 1u << lane;
+	asm volatile( "" : "+r"( lanebit ) ); // kept in a register (else rebuilt with a shift at every block visit)
 
 	const uint2 range = tile_range[tile_id];
 	const unsigned start = range.x, end = range.y;
@@ -124,9 +135,20 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 					continue;
 				const bool cov = ( wl & lanebit ) != 0u; // covered (main.cpp:492-514) and live (:520)
 				if( COUNT )
+				{
 					nlive += cov ? 1u : 0u;
+					if( visit_hist && lane == 0 )
+					{
+						atomicAdd( &g_visit_hist[0][__popc( wl )], 1ull );
+						unsigned tl = 0;
+#pragma unroll
+						for( int jj = 0; jj < 8; jj++ )
+							tl += __popc( live[jj] );
+						atomicAdd( &g_visit_hist[1][min( 32u, ( tl + 7u ) / 8u )], 1ull );
+					}
+				}
 				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
-				const float vy = xsub( fpy0 + (float)( 4 * ( j >> 1 ) ), q0.y );
+				const float vy = xsub( fpyr[j >> 1], q0.y );
 				// d2 = dot( v, inv_cov * v ), main.cpp:526 (inv_cov[0][1] == inv_cov[1][0] == b)
 				const float rx = xadd( avx, xmul( q0.w, vy ) );
 				const float ry = xadd( bvx, xmul( q1.x, vy ) );
@@ -134,8 +156,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 				// exp_approx( -0.5f * d2 ), main.cpp:49-83 (see gauss_of_d2), and alpha, main.cpp:527
 				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
 				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
-				const bool on = cov && !( t < 0.00001814586175896693021059036255f );
-				const float alpha = on ? xmul( t8, op ) : 0.0f;
+				// alpha = ( cov && !( t < threshold ) ) ? t8 * op : 0 with the two conditions folded into one predicate
+				const float alpha = select_alpha( wl & lanebit, t, xmul( t8, op ) );
 				Cr[j] = xadd( Cr[j], xmul( xmul( T[j], q1.y ), alpha ) );   // main.cpp:529-531
 				Cg[j] = xadd( Cg[j], xmul( xmul( T[j], q1.z ), alpha ) );
 				Cb[j] = xadd( Cb[j], xmul( xmul( T[j], q1.w ), alpha ) );
@@ -190,23 +212,39 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 	if( rows <= 0 || g.tiles_x <= 0 )
 		return 0;
 	dim3 grid( g.tiles_x, rows, g.n_images );
+	const int vh = gs2d_tune( "GS2D_VISIT_HIST", 0 );
 #define LAUNCH_FWD( MINB )                                                                                            \
 	do                                                                                                                \
 	{                                                                                                                 \
 		if( count_live )                                                                                              \
 			k_forward<MINB, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image, \
-			                                           b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state );       \
+			                                           b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state, vh );   \
 		else                                                                                                          \
 			k_forward<MINB, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,         \
 			                                            b.image, b.cover, b.loss_partial, b.live_slots, b.staged_slots,        \
-			                                            b.state );                                                    \
+			                                            b.state, 0 );                                                 \
 	} while( 0 )
 	switch( gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) )
 	{
-	case 32: LAUNCH_FWD( 32 ); break;
+	case 24: LAUNCH_FWD( 24 ); break;
 	case 20: LAUNCH_FWD( 20 ); break;
-	default: LAUNCH_FWD( 24 ); break;
+	default: LAUNCH_FWD( 32 ); break;
 	}
 #undef LAUNCH_FWD
 	return 1;
+}
+
+// developer statistic, see g_visit_hist
+extern "C" int gs2d_debug_visit_hist( unsigned long long out[66], int reset )
+{
+	if( !out )
+		return GS2D_ERR_INVALID;
+	if( cudaMemcpyFromSymbol( out, g_visit_hist, sizeof( unsigned long long ) * 66 ) != cudaSuccess )
+		return GS2D_ERR_CUDA;
+	if( reset )
+	{
+		unsigned long long z[66] = { 0 };
+		cudaMemcpyToSymbol( g_visit_hist, z, sizeof( z ) );
+	}
+	return GS2D_OK;
 }

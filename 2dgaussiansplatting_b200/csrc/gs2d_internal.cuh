@@ -20,8 +20,8 @@
 #define GS2D_BATCH 32         // list entries staged into shared memory per round
 #define GS2D_NPLANES 9
 #define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
-#define GS2D_FWD_MINB_DEFAULT 24 // resident warps per SM the forward blend is register-capped for (env GS2D_FWD_MINB)
-#define GS2D_BWD_MINB_DEFAULT 20 // same for the backward blend (env GS2D_BWD_MINB)
+#define GS2D_FWD_MINB_DEFAULT 32 // resident warps per SM the forward blend is register-capped for (env GS2D_FWD_MINB)
+#define GS2D_BWD_MINB_DEFAULT 24 // same for the backward blend (env GS2D_BWD_MINB)
 
 enum
 {
