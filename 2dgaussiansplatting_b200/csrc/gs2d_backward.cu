@@ -86,7 +86,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	const unsigned tile_id = (unsigned)( ( img * g.tiles_y + tile_y ) * g.tiles_x + tile_x );
 	const int tile_x0 = tile_x * GS2D_TILE, tile_y0 = tile_y * GS2D_TILE;
 	const int px_x = tile_x0 + ( lane & 7 ), px_y = tile_y0 + ( lane >> 3 );
-	const float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
+	float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
+	asm volatile( "" : "+f"( fpx0 ), "+f"( fpx1 ) ); // kept in registers (else rebuilt from the integer per entry)
 	const float fpy0 = (float)px_y + 0.5f;
 	// row coordinates and lane bit kept in registers (see k_forward)
 	float fpyr[4] = { fpy0, fpy0 + 4.0f, fpy0 + 8.0f, fpy0 + 12.0f };

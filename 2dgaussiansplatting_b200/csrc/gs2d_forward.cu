@@ -42,7 +42,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 	const int tile_x0 = tile_x * GS2D_TILE, tile_y0 = tile_y * GS2D_TILE;
 	const int px_x = tile_x0 + ( lane & 7 ), px_y = tile_y0 + ( lane >> 3 ); // slot j: x + 8*(j&1), y + 4*(j>>1)
 	// glm::vec2 p = { x + 0.5f, y + 0.5f }, main.cpp:523 (small integers + 0.5 are exact, so is adding 4 or 8)
-	const float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
+	float fpx0 = (float)px_x + 0.5f, fpx1 = fpx0 + 8.0f;
+	asm volatile( "" : "+f"( fpx0 ), "+f"( fpx1 ) ); // kept in registers (else rebuilt from the integer per entry)
 	const float fpy0 = (float)px_y + 0.5f;
 	// the four row coordinates of a lane, kept in registers (opaque to the compiler, which would otherwise rebuild
 	// them from the integer at every block visit: I2FP + 2 FADD)
