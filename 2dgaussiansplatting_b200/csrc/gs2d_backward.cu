@@ -65,6 +65,38 @@ __device__ __forceinline__ void gather_cover( TileSmem<2>& sm, int stage, int la
 	}
 }
 
+// Totals of the n (<= STAGE_SLOTS) entries parked in the staging area: lane (half = lane >> 4, slot = (lane >> 3) & 1,
+// value = lane & 7) adds 16 of the 32 lane-partials of one value of one entry, one shuffle joins the halves. A slot is
+// padded by 8 floats and the halves are 16 lanes apart, so the 32 lanes of a load hit 32 different banks
+// ((8 slot + 8 l + value) mod 32 over half * 128) with plain immediate offsets. The totals go to
+// words_of_stage[k][value], k = the entry's list position.
+#define STAGE_SLOTS 2
+#define STAGE_STRIDE ( 32 * 8 + 8 )
+__device__ __forceinline__ void reduce_group( const float ( *stg )[STAGE_STRIDE], unsigned* words_of_stage,
+                                              unsigned grp_k, unsigned n, int lane )
+{
+	__syncwarp();
+	const unsigned half = (unsigned)lane >> 4, slot = ( (unsigned)lane >> 3 ) & 1u, val = (unsigned)lane & 7u;
+	const float* src = &stg[slot][half * 128u + val];
+	float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+#pragma unroll
+	for( int l = 0; l < 16; l += 4 )
+	{
+		s0 += src[l * 8];
+		s1 += src[l * 8 + 8];
+		s2 += src[l * 8 + 16];
+		s3 += src[l * 8 + 24];
+	}
+	float tot = ( s0 + s1 ) + ( s2 + s3 );
+	tot += __shfl_xor_sync( 0xffffffffu, tot, 16 );
+	if( half == 0u && slot < n )
+	{
+		const unsigned k = ( grp_k >> ( 8u * slot ) ) & 0xffu;
+		words_of_stage[k * 8u + val] = __float_as_uint( tot );
+	}
+	__syncwarp();
+}
+
 template <int MINB, bool OPACITY, bool COUNT>
 __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
                                                               const unsigned* __restrict__ vals,
@@ -79,7 +111,13 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	if( st->need_capacity )
 		return;
 	__shared__ TileSmem<2> sm;
-	__shared__ __align__( 16 ) float part[GS2D_BATCH][OPACITY ? 12 : 8]; // per-entry totals: 3 colour sums, 5 moments (, opacity)
+	// Cross-lane sums. Every lane parks its 8 partial sums of a visited entry here (two 128-bit stores); after two
+	// entries the warp adds them up transposed (reduce_group: 16 conflict-free loads + adds and one shuffle for two
+	// entries, where a shuffle butterfly costs ~45 instructions per entry).
+	// The totals of entry k overwrite its own coverage words sm.words[stage][k][0..7], which are dead once the entry
+	// has been walked - so no separate array is needed for them.
+	__shared__ __align__( 16 ) float stage4[STAGE_SLOTS][STAGE_STRIDE]; // [slot][lane * 8 + value], padded
+	__shared__ float vop_tot[OPACITY ? GS2D_BATCH : 1]; // per-entry total of the opacity gradient
 
 	const int lane = threadIdx.x;
 	const int tile_x = blockIdx.x, tile_y = blockIdx.y + g.band_ty0, img = blockIdx.z;
@@ -162,6 +200,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		unsigned ent = touching_entries( sm, stage, nb, lane, cwa, cwb );
 
 		unsigned visited = 0;
+		unsigned grp_n = 0u, grp_k = 0u; // visited entries parked in stage4, their list positions (8 bits each)
 #pragma unroll 1
 		while( ent )
 		{
@@ -242,25 +281,36 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			v[5] = fmaf( vx0, w0, vx1 * w1 );                // sum w*vx^2
 			v[6] = fmaf( vx0, A1[0], vx1 * A1[1] );          // sum w*vx*vy
 			v[7] = A2;                                       // sum w*vy^2
-			const float r8 = warp_reduce8( v, lane );
-			if( ( lane & 3 ) == 0 )
-				part[k][lane >> 2] = r8;
+			{
+				float4* dst = reinterpret_cast<float4*>( &stage4[grp_n][lane * 8] );
+				dst[0] = make_float4( v[0], v[1], v[2], v[3] );
+				dst[1] = make_float4( v[4], v[5], v[6], v[7] );
+			}
+			grp_k |= (unsigned)k << ( 8u * grp_n );
 			if( OPACITY )
 			{
 #pragma unroll
 				for( int o = 16; o > 0; o >>= 1 )
 					vop += __shfl_xor_sync( 0xffffffffu, vop, o );
 				if( lane == 0 )
-					part[k][8] = vop;
+					vop_tot[k] = vop;
+			}
+			if( ++grp_n == (unsigned)STAGE_SLOTS )
+			{
+				reduce_group( stage4, &sm.words[stage][0][0], grp_k, (unsigned)STAGE_SLOTS, lane );
+				grp_n = 0u;
+				grp_k = 0u;
 			}
 		}
+		if( grp_n )
+			reduce_group( stage4, &sm.words[stage][0][0], grp_k, grp_n, lane );
 		__syncwarp();
 
 		// flush: lane k owns entry k. d{pos,sx,sy,rot} from the moments (main.cpp:635-685), one atomic per parameter.
 		if( ( visited >> lane ) & 1u )
 		{
-			const float4 m0 = *reinterpret_cast<const float4*>( &part[lane][0] ); // dcr dcg dcb Mx
-			const float4 m1 = *reinterpret_cast<const float4*>( &part[lane][4] ); // My Mxx Mxy Myy
+			const float4 m0 = *reinterpret_cast<const float4*>( &sm.words[stage][lane][0] ); // dcr dcg dcb Mx
+			const float4 m1 = *reinterpret_cast<const float4*>( &sm.words[stage][lane][4] ); // My Mxx Mxy Myy
 			const SplatRec& s = sm.rec[stage][lane];
 			const float a = s.a, b = s.b, d = s.d;
 			const float c = s.cosT, sn = s.sinT;
@@ -280,7 +330,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			atomicAdd( gp + PL_SY * np, s.isy3 * ( fmaf( s2, Mxx, fmaf( c2, Myy, -tsc ) ) ) );
 			atomicAdd( gp + PL_ROT * np, s.rotc * ( fmaf( c2 - s2, Mxy, -sc * ( Mxx - Myy ) ) ) );
 			if( OPACITY )
-				atomicAdd( gp + PL_OP * np, part[lane][8] );
+				atomicAdd( gp + PL_OP * np, vop_tot[lane] );
 		}
 
 		unsigned anylive = 0;
