@@ -43,7 +43,7 @@ ABI_SYMBOLS = [
     "gs2d_default_params", "gs2d_version", "gs2d_strerror", "gs2d_last_error", "gs2d_create", "gs2d_destroy",
     "gs2d_set_target_rgba32f", "gs2d_set_target_rgba8", "gs2d_init_reference", "gs2d_upload_state",
     "gs2d_download_state", "gs2d_set_optimize_opacity", "gs2d_step", "gs2d_forward", "gs2d_backward", "gs2d_adam",
-    "gs2d_download_image_rgba32f", "gs2d_download_grads", "gs2d_last_mse", "gs2d_get_stats", "gs2d_comm_unique_id",
+    "gs2d_download_image_rgba32f", "gs2d_download_grads", "gs2d_last_mse", "gs2d_mse_ticket", "gs2d_mse_wait", "gs2d_get_stats", "gs2d_comm_unique_id",
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
     "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
@@ -109,6 +109,8 @@ def load_library():
     L.gs2d_download_image_rgba32f.argtypes = [vp, i, vp]
     L.gs2d_download_grads.argtypes = [vp, i, vp]
     L.gs2d_last_mse.argtypes = [vp, vp]
+    L.gs2d_mse_ticket.argtypes = [vp, C.POINTER(C.c_uint64)]
+    L.gs2d_mse_wait.argtypes = [vp, C.c_uint64, vp]
     L.gs2d_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.gs2d_comm_unique_id.argtypes = [vp]
     L.gs2d_comm_init.argtypes = [vp, i, i, vp]
@@ -305,6 +307,18 @@ class Fitter:
     def last_mse(self):
         out = np.zeros(self.n_images, np.float64)
         self._ck(self.lib.gs2d_last_mse(self._ctx, _ptr(out)))
+        return out
+
+    def mse_ticket(self):
+        """Enqueue the read-back of the newest enqueued iteration's loss; returns a ticket for mse_wait()."""
+        t = C.c_uint64()
+        self._ck(self.lib.gs2d_mse_ticket(self._ctx, C.byref(t)))
+        return t.value
+
+    def mse_wait(self, ticket):
+        """Block until the ticket's copy has landed (later iterations keep running); mse[n_images]."""
+        out = np.zeros(self.n_images, np.float64)
+        self._ck(self.lib.gs2d_mse_wait(self._ctx, C.c_uint64(ticket), _ptr(out)))
         return out
 
     def stats(self):

@@ -464,6 +464,25 @@ int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaS
 	                                                                   n_px );
 	return 1;
 }
+// gs2d_mse_ticket: the loop-carried scalars and the loss of the newest iteration, stored straight into a slot of
+// mapped page-locked host memory (no copy engine involved: a small D2H copy can queue behind a large target upload).
+__global__ void k_publish( const DevState* __restrict__ st, const double* __restrict__ loss, int n_images,
+                           unsigned* __restrict__ slot_state, double* __restrict__ slot_loss )
+{
+	const unsigned* src = reinterpret_cast<const unsigned*>( st );
+	for( int i = threadIdx.x; i < (int)( sizeof( DevState ) / sizeof( unsigned ) ); i += blockDim.x )
+		slot_state[i] = src[i];
+	for( int i = threadIdx.x; i < n_images; i += blockDim.x )
+		slot_loss[i] = loss[i];
+	__threadfence_system();
+}
+int launch_publish( const Buffers& b, int n_images, unsigned char* slot, cudaStream_t s )
+{
+	static_assert( sizeof( DevState ) % sizeof( double ) == 0, "the loss follows the state in a ticket slot" );
+	k_publish<<<1, 64, 0, s>>>( b.state, b.loss, n_images, reinterpret_cast<unsigned*>( slot ),
+	                            reinterpret_cast<double*>( slot + sizeof( DevState ) ) );
+	return 1;
+}
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s )
 {
 	k_finalize_loss<<<g.n_images, LOSS_THREADS, 0, s>>>( g, b.loss_partial, b.loss, b.live_slots, b.stats, b.state );

@@ -141,6 +141,20 @@ struct gs2d_ctx
 	int graph_nodes = 0;
 
 	long long expected_iteration = 0; // what the device counter will read once everything enqueued has run
+
+	// pipelined loss read-back (gs2d_mse_ticket / gs2d_mse_wait): a ring of mapped page-locked slots; a one-block
+	// kernel enqueued behind an iteration stores { DevState, loss[n_images] } into one, an event follows it
+	static const int N_TICKETS = 8;
+	struct Ticket
+	{
+		cudaEvent_t ev = nullptr;
+		uint64_t id = 0;
+		long long expected = 0; // iteration counter the copy must show if nothing was skipped
+	};
+	Ticket tickets[N_TICKETS];
+	uint64_t next_ticket = 1;
+	unsigned char* ticket_pin = nullptr;
+	size_t ticket_stride = 0;
 	cudaEvent_t ev[10]{};
 	float last_ms = 0.0f;
 
@@ -327,6 +341,11 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	}
 	if( c->iter_graph )
 		cudaGraphExecDestroy( c->iter_graph );
+	for( auto& t : c->tickets )
+		if( t.ev )
+			cudaEventDestroy( t.ev );
+	if( c->ticket_pin )
+		cudaFreeHost( c->ticket_pin );
 	for( void* p : c->ipc_opened )
 		cudaIpcCloseMemHandle( p );
 	if( c->comm && g_nccl.CommDestroy )
@@ -1202,6 +1221,56 @@ extern "C" int gs2d_last_mse( gs2d_ctx* c, double* mse )
 	for( int i = 0; i < c->g.n_images; i++ )
 		mse[i] = src[i] / (double)( c->g.H * c->g.W * 3 ); // main.cpp:805
 	return GS2D_OK;
+}
+
+// Pipelined read-back: the caller enqueues iteration i+1 before it waits for the loss of iteration i, so the device
+// never idles across the host round trip. The copies ride the compute stream right behind the iteration they belong
+// to; waiting is on the ticket's own event, not on the stream.
+extern "C" int gs2d_mse_ticket( gs2d_ctx* c, uint64_t* ticket )
+{
+	if( !c || !ticket )
+		return GS2D_ERR_INVALID;
+	CK( cudaSetDevice( c->device ) );
+	if( !c->ticket_pin )
+	{
+		c->ticket_stride = ( sizeof( DevState ) + sizeof( double ) * (size_t)c->g.n_images + 63 ) / 64 * 64;
+		CK( cudaHostAlloc( (void**)&c->ticket_pin, c->ticket_stride * gs2d_ctx::N_TICKETS, cudaHostAllocMapped ) );
+		for( auto& t : c->tickets )
+			CK( cudaEventCreateWithFlags( &t.ev, cudaEventDisableTiming ) );
+	}
+	const uint64_t id = c->next_ticket++;
+	gs2d_ctx::Ticket& t = c->tickets[id % gs2d_ctx::N_TICKETS];
+	unsigned char* slot = c->ticket_pin + ( id % gs2d_ctx::N_TICKETS ) * c->ticket_stride;
+	c->launches += launch_publish( c->b, c->g.n_images, slot, c->stream ); // stores into mapped host memory
+	CK( cudaEventRecord( t.ev, c->stream ) );
+	t.id = id;
+	t.expected = c->expected_iteration;
+	*ticket = id;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_mse_wait( gs2d_ctx* c, uint64_t ticket, double* mse )
+{
+	if( !c || !mse || ticket == 0 )
+		return GS2D_ERR_INVALID;
+	gs2d_ctx::Ticket& t = c->tickets[ticket % gs2d_ctx::N_TICKETS];
+	if( t.id != ticket )
+	{
+		snprintf( c->err, sizeof( c->err ), "mse ticket %llu is unknown or older than the %d newest", (unsigned long long)ticket,
+		          gs2d_ctx::N_TICKETS );
+		return GS2D_ERR_INVALID;
+	}
+	CK( cudaSetDevice( c->device ) );
+	CK( cudaEventSynchronize( t.ev ) );
+	const unsigned char* slot = c->ticket_pin + ( ticket % gs2d_ctx::N_TICKETS ) * c->ticket_stride;
+	DevState s;
+	memcpy( &s, slot, sizeof( s ) );
+	if( s.peer_fault || s.need_capacity || (long long)s.iteration < t.expected )
+		return gs2d_last_mse( c, mse ); // an iteration was skipped (list capacity): recover, report the newest loss
+	const double* loss = reinterpret_cast<const double*>( slot + sizeof( DevState ) );
+	for( int i = 0; i < c->g.n_images; i++ )
+		mse[i] = loss[i] / (double)( c->g.H * c->g.W * 3 ); // main.cpp:805
+	return s.nonfinite ? GS2D_ERR_NONFINITE : GS2D_OK;
 }
 
 extern "C" int gs2d_get_stats( gs2d_ctx* c, gs2d_stats* out )

@@ -188,6 +188,7 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, bool count_live,
                      cudaStream_t s );
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
+int launch_publish( const Buffers& b, int n_images, unsigned char* slot_mapped_host, cudaStream_t s );
 int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
 int launch_adam( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
 // Fused gradient reduction + Adam + parameter broadcast over peer memory (NVLink / NVSwitch, CUDA IPC mappings):

@@ -253,21 +253,35 @@ def run_ours(args):
 
     # ---- end to end through the C ABI with host buffers: `e2e` --------------------------------------------------
     # Every step copies its input (the RGBA8 target; this rank's band of it when sharded) from pinned host memory and
-    # reads its result (the mse) back. The upload of step i+1 is issued while step i runs (gs2d_set_target_rgba8_async:
-    # own copy stream, two staging buffers), as a caller streaming targets would do; nothing else overlaps.
-    Ke = max(3, min(K, args.e2e_steps))
+    # reads its result (the mse) back. Software pipeline of depth one, as a caller streaming targets would write it:
+    # the upload of step i+1 is issued while step i runs (gs2d_set_target_rgba8_async: own copy stream, two staging
+    # buffers), and the mse of step i is waited for (gs2d_mse_wait on its ticket) after step i+1 has been enqueued,
+    # so the device does not idle across the host round trip. Every step's upload and read-back are inside the
+    # timed region; the last step's read-back closes it.
+    # Both loops run the SAME iterations of the fit as the device-resident pass (restart + the same warm-up): the
+    # work per iteration drifts as the fit converges, so a pass over later iterations would not be comparable.
+    Ke = max(3, min(K, args.e2e_steps)) if args.e2e_steps > 0 else K
     h2d_bytes = fit.target_bytes_per_upload()
+    fit.restart()
+    fit.step(max(W, 3))
     fit.set_target_u8_ptr_async(pinned_u8.data_ptr())  # pipeline fill: the target of the first timed step
     barrier()
     t0 = time.perf_counter()
-    mse_last = None
+    mse_last, prev = None, None
     for _ in range(Ke):
         fit.step(1, want_mse=False)                         # enqueue the step (its target was uploaded before)
+        ticket = fit.mse_ticket()                           # D2H of this step's result, enqueued behind it
         fit.set_target_u8_ptr_async(pinned_u8.data_ptr())   # H2D of the next step's input, overlapping this step
-        mse_last = fit.last_mse()                           # blocks; D2H of this step's result
+        if prev is not None:
+            mse_last = fit.mse_wait(prev)                   # blocks on the PREVIOUS step's result only
+        prev = ticket
+    mse_last = fit.mse_wait(prev)
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / Ke
     # the same without the overlap (blocking upload, then the step), for the record
+    fit.restart()
+    fit.step(max(W, 3))
+    barrier()
     t0 = time.perf_counter()
     for _ in range(Ke):
         fit.set_target_u8_ptr(pinned_u8.data_ptr())
@@ -336,10 +350,11 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
         "clocks": clocks, "wall_ms_per_step": wall_ms / K,
         "e2e": {"value": 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d_bytes * world,
-                "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms, "steps": Ke,
+                "d2h_bytes_per_step": (8 + 40) * world, "ms_per_step": e2e_ms, "steps": Ke,
                 "serial_ms_per_step": e2e_serial_ms,
                 "what": "per step and rank: gs2d_step(1) enqueued, gs2d_set_target_rgba8_async of the next step's "
-                        "target from pinned host memory (this rank's band), gs2d_last_mse (blocking D2H); "
+                        "target from pinned host memory (this rank's band), gs2d_mse_ticket for this step (D2H of the "
+                        "loss and the 40-byte device state) and gs2d_mse_wait (blocking) for the previous one; "
                         "serial_ms_per_step = blocking gs2d_set_target_rgba8 then gs2d_step(1, &mse)"},
         "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "last_mse": float(mse_last[0]) if mse_last is not None else None,
@@ -372,7 +387,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--size", type=int, default=4096)
     ap.add_argument("--splats", type=int, default=1_000_000)
-    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end loops (0 = --steps)")
     ap.add_argument("--cpu-iters", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -146,6 +146,16 @@ int gs2d_download_grads( gs2d_ctx* ctx, int image, gs2d_splat* dsplats );  /* ==
 int gs2d_last_mse( gs2d_ctx* ctx, double* mse /* n_images */ );            /* loss of the last forward */
 int gs2d_get_stats( gs2d_ctx* ctx, gs2d_stats* out );                      /* counters of the last forward */
 
+/* Pipelined loss read-back for callers that stream targets (the reference prints the mse of EVERY frame,
+ * main.cpp:807; reading it with gs2d_last_mse drains the device once per iteration). gs2d_mse_ticket enqueues, behind
+ * everything enqueued so far, a device->host copy of the loss of the newest enqueued iteration and returns at once;
+ * gs2d_mse_wait blocks until THAT copy has landed (iterations enqueued after the ticket keep running) and returns
+ * the same value gs2d_last_mse would have returned at the ticket's position in the stream. The 8 newest tickets
+ * can be waited for; an older one returns GS2D_ERR_INVALID. If an iteration had to be re-run because the key
+ * buffers grew, the wait falls back to gs2d_last_mse (newest loss). */
+int gs2d_mse_ticket( gs2d_ctx* ctx, uint64_t* ticket );
+int gs2d_mse_wait( gs2d_ctx* ctx, uint64_t ticket, double* mse /* n_images */ );
+
 /* Tile-row band sharding across ranks (BASELINE config 3/4): this context renders and back-propagates only tile
  * rows [rank*ceil(R/n), ...) of every image; gradients and the loss are summed over ranks before Adam.
  * gs2d_comm_unique_id fills a 128-byte NCCL id on rank 0; the caller ships it to the other ranks (any transport)

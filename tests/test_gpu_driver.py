@@ -141,3 +141,44 @@ def test_async_target_upload_equals_blocking():
         a.set_target_u8(t[0])
         a.restart()
         assert np.allclose(a.step(1), b.step(1), rtol=1e-9)
+
+
+def test_mse_tickets_pipeline():
+    """gs2d_mse_ticket / gs2d_mse_wait: the loss of iteration i read while iteration i+1 is already enqueued equals
+    the loss gs2d_step returns for iteration i; waits may come late and out of order; old tickets expire."""
+    W, H, N, K = 300, 200, 500, 12
+    rng = np.random.default_rng(9)
+    target = rng.integers(0, 256, (H, W, 4), dtype=np.uint8)
+    with gs2d.Fitter(W, H, N) as a, gs2d.Fitter(W, H, N) as b:
+        for f in (a, b):
+            f.set_target_u8(target)
+            f.restart()
+        ref = a.step(K)[:, 0]
+        got, prev = [], None
+        for i in range(K):
+            b.step(1, want_mse=False)
+            t = b.mse_ticket()
+            if prev is not None:
+                got.append(b.mse_wait(prev)[0])  # iteration i-1, while iteration i runs
+            prev = t
+        got.append(b.mse_wait(prev)[0])
+        # two fits of the same problem agree to ~1e-10 only (float atomics sum the gradients in arrival order)
+        assert got[0] == ref[0] and np.allclose(got, ref, rtol=1e-8, atol=0), (np.asarray(got) - ref, ref)
+        assert b.last_mse()[0] == got[-1]
+        # late and out of order: two tickets, the newer one first; a ticket can be waited for twice
+        b.step(1, want_mse=False)
+        t1 = b.mse_ticket()
+        b.step(1, want_mse=False)
+        t2 = b.mse_ticket()
+        m2, m1 = b.mse_wait(t2)[0], b.mse_wait(t1)[0]
+        ref2 = a.step(2)[:, 0]
+        assert np.allclose([m1, m2], ref2, rtol=1e-8, atol=0) and m1 != m2
+        assert b.mse_wait(t1)[0] == m1
+        # nine tickets later the slot of t1 has been reused
+        for _ in range(9):
+            b.mse_ticket()
+        with pytest.raises(gs2d.Gs2dError) as e:
+            b.mse_wait(t1)
+        assert e.value.code == -1
+        with pytest.raises(gs2d.Gs2dError):
+            b.mse_wait(0)
