@@ -135,88 +135,97 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		const float sy = params[PL_SY * g.n_pad + gi];
 		const float rot = params[PL_ROT * g.n_pad + gi];
 
-		// cosf/sinf of the reference are glibc's (< 1 ulp, almost always correctly rounded). Evaluate in double and
-		// round once: agrees with it bit for bit except in rare double-rounding cases.
-		double sd, cd;
-		sincos( (double)rot, &sd, &cd );
-		const float c = (float)cd, s = (float)sd;
-
-		// cov_of, main.cpp:214-220
-		const float l0 = xmul( sx, sx );
-		const float l1 = xmul( sy, sy );
-		const float s11 = xadd( xmul( xmul( l0, c ), c ), xmul( xmul( l1, s ), s ) );
-		const float s12 = xmul( xmul( xsub( l0, l1 ), s ), c );
-		const float s22 = xsub( xadd( l0, l1 ), s11 );
-		const float det = xsub( xmul( s11, s22 ), xmul( s12, s12 ) ); // main.cpp:191, :560
-		// inv_cov = mat2( cov[1][1], -cov[0][1], -cov[1][0], cov[0][0] ) / det, main.cpp:432-436
-		const float a = xdiv( s22, det );
-		const float b = xdiv( -s12, det );
-		const float d = xdiv( s11, det );
-		// row range, main.cpp:489-491
-		const float h = xmul( xsqrt( xmul( a, det ) ), 3.0f );
-		const int begY = trunc_x86( xsub( py, h ) );
-		const int endY = trunc_x86( xadd( py, h ) );
-
-		SplatRec r;
-		r.px = px;
-		r.py = py;
-		r.a = a;
-		r.b = b;
-		r.d = d;
-		r.cr = params[PL_CR * g.n_pad + gi];
-		r.cg = params[PL_CG * g.n_pad + gi];
-		r.cb = params[PL_CB * g.n_pad + gi];
-		r.op = params[PL_OP * g.n_pad + gi];
-		r.begY = begY;
-		r.endY = endY;
-		// hoisted backward invariants, main.cpp:658, :661, :682 (same operand order)
-		r.rotc = xdiv( xsub( xmul( sx, sx ), xmul( sy, sy ) ), xmul( xmul( xmul( sx, sx ), sy ), sy ) );
-		r.cosT = c;
-		r.sinT = s;
-		r.isx3 = xdiv( 1.0f, xmul( xmul( sx, sx ), sx ) );
-		r.isy3 = xdiv( 1.0f, xmul( xmul( sy, sy ), sy ) );
-		float4* dst = reinterpret_cast<float4*>( rec + gi );
-		const float4* src = reinterpret_cast<const float4*>( &r );
-		dst[0] = src[0];
-		dst[1] = src[1];
-		dst[2] = src[2];
-		dst[3] = src[3];
-
-		// Conservative tile rectangle. Rows: exactly the reference's [begY, endY]. Columns: every chord of the 3-sigma
-		// ellipse lies within pos.x +- 3*sqrt(cov[0][0]) = 3*sqrt(d*det); widened by 2 px + 1e-4 relative for the
-		// truncation rule and the float error of the quadratic solve. Only a superset is needed here: the exact
-		// per-pixel set is decided by row_mask() in the forward blend.
-		const int H = g.H, W = g.W;
-		const int y0 = max( begY, 0 ), y1 = min( endY, H - 1 );
-		const float hx = xmul( xsqrt( xmul( d, det ) ), 3.0f );
-		const float m = 2.0f + hx * 1.0e-4f;
-		const float fx0 = floorf( px - hx - m ), fx1 = floorf( px + hx + m );
-		const int x0 = ( fx0 == fx0 ) ? (int)fmaxf( fx0, 0.0f ) : 0;
-		int x1 = ( fx1 == fx1 ) ? (int)fminf( fx1, (float)( W - 1 ) ) : W - 1;
-		if( fx1 < 0.0f )
-			x1 = -1;
-		if( y0 <= y1 && x0 <= x1 )
+		// A rank that owns a band of tile rows skips the splats that cannot reach it before any of the expensive
+		// work (double sincos, five IEEE divisions, the 64-byte record, which only this rank's blend would read):
+		// cov[1][1] <= max(sx, sy)^2 whatever the rotation, so the reference's rows lie within py +- 3 max(sx, sy);
+		// 2 px and 1e-3 relative cover the truncation and the float error of the exact bound. NaNs fall through.
+		const float hmax = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f;
+		const bool off_band = py + hmax < (float)( g.band_ty0 * GS2D_TILE ) || py - hmax > (float)( g.band_ty1 * GS2D_TILE );
+		if( !off_band )
 		{
-			sb.ty0 = max( y0 / GS2D_TILE, g.band_ty0 );
-			sb.ty1 = min( y1 / GS2D_TILE, g.band_ty1 - 1 );
-			sb.rtx0 = x0 / GS2D_TILE;
-			sb.rtx1 = x1 / GS2D_TILE;
+			// cosf/sinf of the reference are glibc's (< 1 ulp, almost always correctly rounded). Evaluate in double and
+			// round once: agrees with it bit for bit except in rare double-rounding cases.
+			double sd, cd;
+			sincos( (double)rot, &sd, &cd );
+			const float c = (float)cd, s = (float)sd;
+
+			// cov_of, main.cpp:214-220
+			const float l0 = xmul( sx, sx );
+			const float l1 = xmul( sy, sy );
+			const float s11 = xadd( xmul( xmul( l0, c ), c ), xmul( xmul( l1, s ), s ) );
+			const float s12 = xmul( xmul( xsub( l0, l1 ), s ), c );
+			const float s22 = xsub( xadd( l0, l1 ), s11 );
+			const float det = xsub( xmul( s11, s22 ), xmul( s12, s12 ) ); // main.cpp:191, :560
+			// inv_cov = mat2( cov[1][1], -cov[0][1], -cov[1][0], cov[0][0] ) / det, main.cpp:432-436
+			const float a = xdiv( s22, det );
+			const float b = xdiv( -s12, det );
+			const float d = xdiv( s11, det );
+			// row range, main.cpp:489-491
+			const float h = xmul( xsqrt( xmul( a, det ) ), 3.0f );
+			const int begY = trunc_x86( xsub( py, h ) );
+			const int endY = trunc_x86( xadd( py, h ) );
+
+			SplatRec r;
+			r.px = px;
+			r.py = py;
+			r.a = a;
+			r.b = b;
+			r.d = d;
+			r.cr = params[PL_CR * g.n_pad + gi];
+			r.cg = params[PL_CG * g.n_pad + gi];
+			r.cb = params[PL_CB * g.n_pad + gi];
+			r.op = params[PL_OP * g.n_pad + gi];
+			r.begY = begY;
+			r.endY = endY;
+			// hoisted backward invariants, main.cpp:658, :661, :682 (same operand order)
+			r.rotc = xdiv( xsub( xmul( sx, sx ), xmul( sy, sy ) ), xmul( xmul( xmul( sx, sx ), sy ), sy ) );
+			r.cosT = c;
+			r.sinT = s;
+			r.isx3 = xdiv( 1.0f, xmul( xmul( sx, sx ), sx ) );
+			r.isy3 = xdiv( 1.0f, xmul( xmul( sy, sy ), sy ) );
+			float4* dst = reinterpret_cast<float4*>( rec + gi );
+			const float4* src = reinterpret_cast<const float4*>( &r );
+			dst[0] = src[0];
+			dst[1] = src[1];
+			dst[2] = src[2];
+			dst[3] = src[3];
+
+			// Conservative tile rectangle. Rows: exactly the reference's [begY, endY]. Columns: every chord of the 3-sigma
+			// ellipse lies within pos.x +- 3*sqrt(cov[0][0]) = 3*sqrt(d*det); widened by 2 px + 1e-4 relative for the
+			// truncation rule and the float error of the quadratic solve. Only a superset is needed here: the exact
+			// per-pixel set is decided by row_mask() in the forward blend.
+			const int H = g.H, W = g.W;
+			const int y0 = max( begY, 0 ), y1 = min( endY, H - 1 );
+			const float hx = xmul( xsqrt( xmul( d, det ) ), 3.0f );
+			const float m = 2.0f + hx * 1.0e-4f;
+			const float fx0 = floorf( px - hx - m ), fx1 = floorf( px + hx + m );
+			const int x0 = ( fx0 == fx0 ) ? (int)fmaxf( fx0, 0.0f ) : 0;
+			int x1 = ( fx1 == fx1 ) ? (int)fminf( fx1, (float)( W - 1 ) ) : W - 1;
+			if( fx1 < 0.0f )
+				x1 = -1;
+			if( y0 <= y1 && x0 <= x1 )
+			{
+				sb.ty0 = max( y0 / GS2D_TILE, g.band_ty0 );
+				sb.ty1 = min( y1 / GS2D_TILE, g.band_ty1 - 1 );
+				sb.rtx0 = x0 / GS2D_TILE;
+				sb.rtx1 = x1 / GS2D_TILE;
+			}
+			const int img = gi / g.n_splats;
+			sb.tile_base = img * g.tiles_y * g.tiles_x;
+			sb.slice = ( gi - img * g.n_splats ) / g.slice_size;
+			sb.local = ( gi - img * g.n_splats ) - sb.slice * g.slice_size;
+			sb.k.px = px;
+			sb.k.py = py;
+			sb.k.a = a;
+			sb.k.b = b;
+			sb.k.d = d;
+			sb.k.inv_a = 1.0f / a;
+			sb.k.vx_max = hx; // 3 * sqrt( cov[0][0] ) == 3 * sqrt( d / (a d - b^2) )
+			sb.k.vy_at = -b * hx / d;
+			sb.k.delta = cull ? 0.02f + 1.0e-3f * hx + 1.0e-6f * fabsf( px ) : __int_as_float( 0x7fc00000 ); // NaN: no culling
+			sb.k.begY = begY;
+			sb.k.endY = endY;
 		}
-		const int img = gi / g.n_splats;
-		sb.tile_base = img * g.tiles_y * g.tiles_x;
-		sb.slice = ( gi - img * g.n_splats ) / g.slice_size;
-		sb.local = ( gi - img * g.n_splats ) - sb.slice * g.slice_size;
-		sb.k.px = px;
-		sb.k.py = py;
-		sb.k.a = a;
-		sb.k.b = b;
-		sb.k.d = d;
-		sb.k.inv_a = 1.0f / a;
-		sb.k.vx_max = hx; // 3 * sqrt( cov[0][0] ) == 3 * sqrt( d / (a d - b^2) )
-		sb.k.vy_at = -b * hx / d;
-		sb.k.delta = cull ? 0.02f + 1.0e-3f * hx + 1.0e-6f * fabsf( px ) : __int_as_float( 0x7fc00000 ); // NaN: no culling
-		sb.k.begY = begY;
-		sb.k.endY = endY;
 	}
 	const bool has = sb.ty0 <= sb.ty1 && sb.rtx0 <= sb.rtx1;
 
