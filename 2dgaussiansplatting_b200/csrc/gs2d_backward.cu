@@ -217,12 +217,12 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				continue;
 			visited |= 1u << k;
 			const SplatRec& s = sm.rec[stage][k];
-			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py a b
-			const float4 q1 = *reinterpret_cast<const float4*>( &s.d );  // d cr cg cb
+			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py b d
+			const float4 q1 = *reinterpret_cast<const float4*>( &s.a );  // a cr cg cb
 			const float op = s.op;
 			const float vx0 = xsub( fpx0, q0.x ), vx1 = xsub( fpx1, q0.x );
-			const float avx0 = xmul( q0.z, vx0 ), avx1 = xmul( q0.z, vx1 );
-			const float bvx0 = xmul( q0.w, vx0 ), bvx1 = xmul( q0.w, vx1 );
+			const float avx0 = xmul( q1.x, vx0 ), avx1 = xmul( q1.x, vx1 );
+			const float bvx0 = xmul( q0.z, vx0 ), bvx1 = xmul( q0.z, vx1 );
 			float gc0 = 0.f, gc1 = 0.f, gc2 = 0.f;          // sum dL/dC * alpha * T            (main.cpp:618-619)
 			float A0[2] = { 0.f, 0.f }, A1[2] = { 0.f, 0.f }; // sum w, sum w*vy per block column   (w = g * alpha)
 			float A2 = 0.f, vop = 0.f;                      // sum w*vy^2; sum g*G               (main.cpp:703-704)
@@ -237,8 +237,10 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 					nlive += cov ? 1u : 0u;
 				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
 				const float vy = xsub( fpyr[j >> 1], q0.y );
-				const float rx = xadd( avx, xmul( q0.w, vy ) );
-				const float ry = xadd( bvx, xmul( q1.x, vy ) );
+				// scalar multiplies here: the packed forms of k_forward need aligned register pairs, which at this
+				// kernel's 80-register cap spill (measured: lane bit reloaded from local memory at every visit)
+				const float rx = xadd( avx, xmul( q0.z, vy ) );
+				const float ry = xadd( bvx, xmul( q0.w, vy ) );
 				const float d2 = xadd( xmul( vx, rx ), xmul( vy, ry ) );
 				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
 				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );

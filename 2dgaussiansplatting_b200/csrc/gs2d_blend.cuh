@@ -28,6 +28,29 @@ __device__ __forceinline__ float select_alpha( unsigned covered, float t, float 
 	return r;
 }
 
+// Two floats in an aligned register pair, and the packed multiply mul.rn.f32x2 (SASS FMUL2): each half is the IEEE
+// product, exactly __fmul_rn, but the pair costs ONE issue slot (the blend kernels are issue-bound).
+// Only multiplies are packed: ptxas contracts a packed multiply feeding a packed add into FFMA2 (one rounding, not
+// the reference's two), whereas a scalar add.rn.f32 of one half is never contracted. A scalar operand is written
+// pack2( s, s ); ptxas encodes it as a broadcast (R.F32), no move.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2( float lo, float hi )
+{
+	f32x2 r;
+	asm( "mov.b64 %0, {%1, %2};" : "=l"( r ) : "f"( lo ), "f"( hi ) );
+	return r;
+}
+__device__ __forceinline__ void unpack2( f32x2 p, float& lo, float& hi )
+{
+	asm( "mov.b64 {%0, %1}, %2;" : "=f"( lo ), "=f"( hi ) : "l"( p ) );
+}
+__device__ __forceinline__ f32x2 xmul2( f32x2 a, f32x2 b )
+{
+	f32x2 r;
+	asm( "mul.rn.f32x2 %0, %1, %2;" : "=l"( r ) : "l"( a ), "l"( b ) );
+	return r;
+}
+
 // WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)
 template <int WSTAGES>
 struct TileSmem

@@ -122,12 +122,13 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 			if( hit == 0u )
 				continue;
 			const SplatRec& s = sm.rec[stage][k];
-			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py a b
-			const float4 q1 = *reinterpret_cast<const float4*>( &s.d );  // d cr cg cb
+			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py b d
+			const float4 q1 = *reinterpret_cast<const float4*>( &s.a );  // a cr cg cb
 			const float op = s.op;
 			const float vx0 = xsub( fpx0, q0.x ), vx1 = xsub( fpx1, q0.x );
-			const float avx0 = xmul( q0.z, vx0 ), avx1 = xmul( q0.z, vx1 );
-			const float bvx0 = xmul( q0.w, vx0 ), bvx1 = xmul( q0.w, vx1 );
+			const float avx0 = xmul( q1.x, vx0 ), avx1 = xmul( q1.x, vx1 );
+			const float bvx0 = xmul( q0.z, vx0 ), bvx1 = xmul( q0.z, vx1 );
+			const f32x2 bd = pack2( q0.z, q0.w ), cgb = pack2( q1.z, q1.w ); // packed multiplies: see xmul2
 #pragma unroll
 			for( int j = 0; j < 8; j++ )
 			{
@@ -151,17 +152,22 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
 				const float vy = xsub( fpyr[j >> 1], q0.y );
 				// d2 = dot( v, inv_cov * v ), main.cpp:526 (inv_cov[0][1] == inv_cov[1][0] == b)
-				const float rx = xadd( avx, xmul( q0.w, vy ) );
-				const float ry = xadd( bvx, xmul( q1.x, vy ) );
-				const float d2 = xadd( xmul( vx, rx ), xmul( vy, ry ) );
+				float bvy, dvy, vxrx, vyry;
+				unpack2( xmul2( bd, pack2( vy, vy ) ), bvy, dvy );
+				const float rx = xadd( avx, bvy );
+				const float ry = xadd( bvx, dvy );
+				unpack2( xmul2( pack2( vx, vy ), pack2( rx, ry ) ), vxrx, vyry );
+				const float d2 = xadd( vxrx, vyry );
 				// exp_approx( -0.5f * d2 ), main.cpp:49-83 (see gauss_of_d2), and alpha, main.cpp:527
 				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
 				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
 				// alpha = ( cov && !( t < threshold ) ) ? t8 * op : 0 with the two conditions folded into one predicate
 				const float alpha = select_alpha( wl & lanebit, t, xmul( t8, op ) );
+				float tga, tba;
+				unpack2( xmul2( xmul2( pack2( T[j], T[j] ), cgb ), pack2( alpha, alpha ) ), tga, tba );
 				Cr[j] = xadd( Cr[j], xmul( xmul( T[j], q1.y ), alpha ) );   // main.cpp:529-531
-				Cg[j] = xadd( Cg[j], xmul( xmul( T[j], q1.z ), alpha ) );
-				Cb[j] = xadd( Cb[j], xmul( xmul( T[j], q1.w ), alpha ) );
+				Cg[j] = xadd( Cg[j], tga );
+				Cb[j] = xadd( Cb[j], tba );
 				T[j] = xmul( T[j], xsub( 1.0f, alpha ) );                   // main.cpp:533
 				live[j] = __ballot_sync( 0xffffffffu, !( T[j] < min_T ) );
 			}

@@ -40,8 +40,8 @@ enum
 // invariants hoisted out of the backward pass (cos, sin, sx^-3, sy^-3, (sx^2-sy^2)/(sx^2 sy^2)).
 struct __align__( 16 ) SplatRec
 {
-	float px, py, a, b;        // q0: position, inv_cov[0][0], inv_cov[1][0] (== inv_cov[0][1])
-	float d, cr, cg, cb;       // q1: inv_cov[1][1], colour
+	float px, py, b, d;        // q0: position, inv_cov[1][0] (== inv_cov[0][1]), inv_cov[1][1]; (b, d) and (cg, cb) sit
+	float a, cr, cg, cb;       // q1: inv_cov[0][0], colour                      in aligned register pairs (xmul2)
 	float op;                  // q2: opacity
 	int begY, endY;            //     row range, main.cpp:490-491 (x86 truncation semantics)
 	float rotc;                //     (sx^2 - sy^2) / (sx^2 sy^2)
