@@ -354,7 +354,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage, c->mbox };
+	                 b.state,      c->dstage, c->mbox,   b.tile_done };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -430,6 +430,9 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	} while( 0 )
 	CKC( cudaSetDevice( device ) );
 	CKC( cudaStreamCreateWithFlags( &c->stream, cudaStreamNonBlocking ) );
+	prepare_forward_pdl();
+	prepare_backward_pdl();
+	cudaGetLastError(); // a refused carveout hint is not an error of this call
 	for( auto& e : c->ev )
 		CKC( cudaEventCreate( &e ) );
 
@@ -476,6 +479,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.loss_partial, sizeof( double ) * (size_t)g.n_tiles_total ) );
+	CKC( cudaMalloc( &b.tile_done, sizeof( unsigned ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.live_slots, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 3 ) );
 	b.staged_slots = b.live_slots + GS2D_LIVE_SLOTS;
 	CKC( cudaMalloc( &b.stats, sizeof( unsigned long long ) * 8 ) );
@@ -933,10 +937,22 @@ static int enqueue_iteration( gs2d_ctx* c )
 	PROF( 0 );
 	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr );
 	PROF( 2 );
-	c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->count_live, s );
-	c->launches += launch_finalize_loss( c->g, c->b, s );
-	PROF( 3 );
-	c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s );
+	if( gs2d_pdl_usable( c->count_live ) )
+	{
+		// forward -> backward overlap (gs2d_blend.cuh): the two grids must be adjacent on the stream, so the loss is
+		// finalised behind the backward pass and profiling group 2 (forward) is empty, group 3 holds both passes
+		PROF( 3 );
+		c->launches += launch_forward( c->g, c->b, c->sorted_buf, false, s, true );
+		c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s, true );
+		c->launches += launch_finalize_loss( c->g, c->b, s );
+	}
+	else
+	{
+		c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->count_live, s );
+		c->launches += launch_finalize_loss( c->g, c->b, s );
+		PROF( 3 );
+		c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s );
+	}
 	PROF( 4 );
 	int rc = enqueue_update( c, pr ? pr->ev[5] : nullptr, false );
 	if( rc )
@@ -1048,7 +1064,7 @@ static int resolve( gs2d_ctx* c )
 		const DevState& s = *c->h_state;
 		if( s.peer_fault )
 		{
-			snprintf( c->err, sizeof( c->err ), "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
+			snprintf( c->err, sizeof( c->err ), s.peer_fault == 2 ? "a forward -> backward tile flag did not arrive (GS2D_PDL)" : "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
 			return GS2D_ERR_NCCL;
 		}
 		const long long missing = c->expected_iteration - (long long)s.iteration;

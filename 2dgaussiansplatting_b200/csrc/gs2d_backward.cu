@@ -97,7 +97,9 @@ __device__ __forceinline__ void reduce_group( const float ( *stg )[STAGE_STRIDE]
 	__syncwarp();
 }
 
-template <int MINB, bool OPACITY, bool COUNT>
+// PDL: launched behind k_forward<.., true> with programmatic stream serialization; waits for its own tile's forward
+// pass instead of the whole grid (gs2d_blend.cuh).
+template <int MINB, bool OPACITY, bool COUNT, bool PDL>
 __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
                                                               const unsigned* __restrict__ vals,
                                                               const uint2* __restrict__ tile_range,
@@ -106,7 +108,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
                                                               const unsigned* __restrict__ cover,
                                                               float* __restrict__ grads,
                                                               unsigned long long* __restrict__ live_slots,
-                                                              const DevState* __restrict__ st )
+                                                              const DevState* __restrict__ st,
+                                                              const unsigned* tile_done )
 {
 	if( st->need_capacity )
 		return;
@@ -140,6 +143,17 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	const unsigned start = range.x, end = range.y;
 	if( start >= end )
 		return;
+	if( PDL )
+	{
+		// tile_range and the lists were complete before k_forward started; the tile's pixels and coverage words are
+		// complete once its forward warp has published the flag
+		if( !pdl_wait_tile( tile_done + tile_id, lane ) )
+		{
+			if( lane == 0 )
+				atomicExch( const_cast<int*>( &st->peer_fault ), 2 );
+			return;
+		}
+	}
 
 	// per-pixel constants dL/dC = final - reference (main.cpp:613-616) and the running state: throughput T of the
 	// prefix (image1.w, main.cpp:549) and Q = sum_c dL/dC_c * (final_c - prefix_c); prefix colour starts at 0.
@@ -154,7 +168,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		if( x < g.W && y < g.H )
 		{
 			const size_t pix = ( (size_t)img * g.H + y ) * g.W + x;
-			const float4 fin = image[pix];
+			const float4 fin = PDL ? __ldcg( image + pix ) : image[pix]; // PDL: written by a grid that is still running
 			const float4 ref = target[pix];
 			dLr[j] = xsub( fin.x, ref.x );
 			dLg[j] = xsub( fin.y, ref.y );
@@ -354,8 +368,45 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	}
 }
 
+template <bool OPACITY>
+static void launch_backward_pdl( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf,
+                                 unsigned long long* slots, cudaStream_t s )
+{
+	auto kernel = k_backward<GS2D_BWD_MINB_DEFAULT, OPACITY, false, true>;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = grid;
+	cfg.blockDim = dim3( 32 );
+	cfg.dynamicSmemBytes = 0;
+	cfg.stream = s;
+	cfg.attrs = attr;
+	cfg.numAttrs = 1;
+	cudaLaunchKernelEx( &cfg, kernel, g, (const SplatRec*)b.rec, (const unsigned*)b.vals[sorted_buf],
+	                    (const uint2*)b.tile_range, (const float4*)b.target, (const float4*)b.image,
+	                    (const unsigned*)b.cover, b.grads, slots, (const DevState*)b.state,
+	                    (const unsigned*)b.tile_done );
+}
+
+void prepare_backward_pdl()
+{
+	cudaFuncSetAttribute( k_backward<GS2D_BWD_MINB_DEFAULT, false, false, true>,
+	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
+	cudaFuncSetAttribute( k_backward<GS2D_BWD_MINB_DEFAULT, true, false, true>,
+	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
+}
+
+// PDL twins exist for the default register caps with the work counters off
+bool gs2d_pdl_usable( bool count_live )
+{
+	return gs2d_tune( "GS2D_PDL", 0 ) != 0 && !count_live &&
+	       gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) == GS2D_FWD_MINB_DEFAULT &&
+	       gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT ) == GS2D_BWD_MINB_DEFAULT;
+}
+
 int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, bool count_live,
-                     cudaStream_t s )
+                     cudaStream_t s, bool pdl )
 {
 	const int rows = g.band_ty1 - g.band_ty0;
 	if( rows <= 0 || g.tiles_x <= 0 )
@@ -365,9 +416,17 @@ int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool w
 	unsigned long long* slots = b.live_slots + 2 * GS2D_LIVE_SLOTS;
 	if( count_live )
 		cudaMemsetAsync( slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS, s );
+	if( pdl )
+	{
+		if( with_opacity )
+			launch_backward_pdl<true>( grid, g, b, sorted_buf, slots, s );
+		else
+			launch_backward_pdl<false>( grid, g, b, sorted_buf, slots, s );
+		return 1;
+	}
 #define LAUNCH_BWD3( MINB, OP, CNT )                                                                                  \
-	k_backward<MINB, OP, CNT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image,     \
-	                                               b.cover, b.grads, slots, b.state )
+	k_backward<MINB, OP, CNT, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,       \
+	                                                      b.image, b.cover, b.grads, slots, b.state, nullptr )
 #define LAUNCH_BWD( MINB )                                                                                            \
 	do                                                                                                                \
 	{                                                                                                                 \

@@ -51,6 +51,48 @@ __device__ __forceinline__ f32x2 xmul2( f32x2 a, f32x2 b )
 	return r;
 }
 
+// ---- forward -> backward overlap through programmatic dependent launch (opt-in: GS2D_PDL=1) -----------------------
+// The blend grids end in a tail: one warp per tile, so the last resident tiles keep their SMs mostly idle for one
+// tile's run time (~50 us; twice per iteration, a quarter of a rank's blend time at N = 8). The backward pass of a
+// tile needs the forward pass of THAT tile only (its final pixels, coverage words), so in this mode
+//   * every forward warp issues griddepcontrol.launch_dependents first thing: the backward grid becomes eligible
+//     once the LAST forward warp has started, i.e. all forward warps already hold their SM slots (no deadlock:
+//     a waiting backward warp can never keep a forward warp from being scheduled);
+//   * the backward grid is launched with the programmatic-stream-serialization attribute and never executes
+//     griddepcontrol.wait (that would wait for the whole forward grid); instead the warp of tile t spins on
+//     tile_done[t], which the forward warp of t stores with release semantics after its last global write.
+// Backward warps are dispatched in tile order, so the tiles they ask for finished long ago; the wait is a single
+// acquire load except for the last wave. What the backward reads of the forward's output goes through L2
+// (cp.async.cg, ld.global.cg): L1 is not coherent with stores of a concurrently running grid.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile( "griddepcontrol.launch_dependents;" ::: "memory" ); }
+__device__ __forceinline__ void pdl_publish_tile( unsigned* flag, int lane )
+{
+	__threadfence(); // this lane's pixel / coverage / loss stores are performed at gpu scope
+	__syncwarp();
+	if( lane == 0 )
+		asm volatile( "st.release.gpu.global.u32 [%0], %1;" ::"l"( flag ), "r"( 1u ) : "memory" );
+}
+// false: the flag did not arrive within ~2 s (cannot happen with the launch order above; never hang the device)
+__device__ __forceinline__ bool pdl_wait_tile( const unsigned* flag, int lane )
+{
+	unsigned ok = 1u;
+	if( lane == 0 )
+	{
+		unsigned v = 0u;
+#pragma unroll 1
+		for( unsigned spin = 0; spin < ( 1u << 22 ); spin++ )
+		{
+			asm volatile( "ld.acquire.gpu.global.u32 %0, [%1];" : "=r"( v ) : "l"( flag ) : "memory" );
+			if( v != 0u )
+				break;
+			__nanosleep( 500 );
+		}
+		ok = v;
+	}
+	ok = __shfl_sync( 0xffffffffu, ok, 0 ); // also orders the other lanes' loads after lane 0's acquire
+	return ok != 0u;
+}
+
 // WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)
 template <int WSTAGES>
 struct TileSmem

@@ -20,7 +20,10 @@
 // per 8x4 block visit, and of the live pixels left in the tile at each visit
 __device__ unsigned long long g_visit_hist[2][33];
 
-template <int MINB, bool COUNT>
+// PDL (GS2D_PDL=1, gs2d_blend.cuh): the backward grid is launched with programmatic stream serialization and fills the
+// SM slots the forward pass's last wave frees; a tile's forward warp publishes tile_done[tile] when its image pixels,
+// coverage words and loss partial are written, and the tile's backward warp waits for exactly that.
+template <int MINB, bool COUNT, bool PDL>
 __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const SplatRec* __restrict__ rec,
                                                              const unsigned* __restrict__ vals,
                                                              const uint2* __restrict__ tile_range,
@@ -30,8 +33,11 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
                                                              double* __restrict__ loss_partial,
                                                              unsigned long long* __restrict__ live_slots,
                                                              unsigned long long* __restrict__ staged_slots,
-                                                             const DevState* __restrict__ st, int visit_hist )
+                                                             const DevState* __restrict__ st, int visit_hist,
+                                                             unsigned* __restrict__ tile_done )
 {
+	if( PDL )
+		pdl_launch_dependents(); // the dependent grid may start once every forward warp has got this far (or exited)
 	if( st->need_capacity )
 		return;
 	__shared__ TileSmem<1> sm;
@@ -210,9 +216,18 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 		atomicAdd( &live_slots[tile_id & ( GS2D_LIVE_SLOTS - 1 )], (unsigned long long)nlive );
 		atomicAdd( &staged_slots[tile_id & ( GS2D_LIVE_SLOTS - 1 )], (unsigned long long)nstaged );
 	}
+	if( PDL )
+		pdl_publish_tile( tile_done + tile_id, lane );
 }
 
-int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s )
+// both PDL blend kernels ask for the same shared-memory carveout, so that warps of the two grids can share an SM
+void prepare_forward_pdl()
+{
+	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+	                      cudaSharedmemCarveoutMaxShared );
+}
+
+int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s, bool pdl )
 {
 	cudaMemsetAsync( b.live_slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS * 2, s );
 	const int rows = g.band_ty1 - g.band_ty0;
@@ -220,16 +235,26 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 		return 0;
 	dim3 grid( g.tiles_x, rows, g.n_images );
 	const int vh = gs2d_tune( "GS2D_VISIT_HIST", 0 );
+	if( pdl ) // only the default variant (32 warps per SM, counters off) has a PDL twin: gs2d_pdl_usable()
+	{
+		cudaMemsetAsync( b.tile_done, 0, sizeof( unsigned ) * (size_t)g.n_tiles_total, s );
+		k_forward<GS2D_FWD_MINB_DEFAULT, false, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
+		                                                                    b.target, b.image, b.cover, b.loss_partial,
+		                                                                    b.live_slots, b.staged_slots, b.state, 0,
+		                                                                    b.tile_done );
+		return 1;
+	}
 #define LAUNCH_FWD( MINB )                                                                                            \
 	do                                                                                                                \
 	{                                                                                                                 \
 		if( count_live )                                                                                              \
-			k_forward<MINB, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image, \
-			                                           b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state, vh );   \
+			k_forward<MINB, true, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,   \
+			                                                  b.image, b.cover, b.loss_partial, b.live_slots,         \
+			                                                  b.staged_slots, b.state, vh, nullptr );                 \
 		else                                                                                                          \
-			k_forward<MINB, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,         \
-			                                            b.image, b.cover, b.loss_partial, b.live_slots, b.staged_slots,        \
-			                                            b.state, 0 );                                                 \
+			k_forward<MINB, false, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,  \
+			                                                   b.image, b.cover, b.loss_partial, b.live_slots,        \
+			                                                   b.staged_slots, b.state, 0, nullptr );                 \
 	} while( 0 )
 	switch( gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) )
 	{

@@ -169,6 +169,7 @@ struct Buffers
 	float4* target;           // [n_images][H][W]
 	float4* image;            // [n_images][H][W]
 	double* loss_partial;     // [n_tiles_total]
+	unsigned* tile_done;      // [n_tiles_total] forward -> backward tile flags of the PDL overlap (gs2d_blend.cuh)
 	unsigned long long* live_slots;   // [GS2D_LIVE_SLOTS]
 	unsigned long long* staged_slots; // [GS2D_LIVE_SLOTS], contiguous after live_slots
 	unsigned long long* stats;        // [2] live pairs, staged entries of the last forward (summed slots)
@@ -184,9 +185,15 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
                                cudaEvent_t after_emit );
 // developer tuning knob: integer environment variable read once per name, else the default
 int gs2d_tune( const char* env_name, int dflt );
-int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s );
+// pdl: forward/backward overlap through programmatic dependent launch (gs2d_blend.cuh); must be set for both or none,
+// backward directly behind forward on the stream, work counters off, default register caps (gs2d_pdl_usable)
+int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s,
+                    bool pdl = false );
 int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, bool count_live,
-                     cudaStream_t s );
+                     cudaStream_t s, bool pdl = false );
+bool gs2d_pdl_usable( bool count_live );
+void prepare_forward_pdl();  // per-device kernel attributes of the PDL twins (called once by gs2d_create)
+void prepare_backward_pdl();
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_publish( const Buffers& b, int n_images, unsigned char* slot_mapped_host, cudaStream_t s );
 int launch_advance( const Geometry& g, const Buffers& b, const gs2d_params& p, cudaStream_t s );
