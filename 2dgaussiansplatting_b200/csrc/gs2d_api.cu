@@ -354,7 +354,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage, c->mbox,   b.tile_done };
+	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -472,7 +472,9 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.adam_v, plane_bytes ) );
 	CKC( cudaMalloc( &b.rec, sizeof( SplatRec ) * (size_t)std::max( g.n_total, 1 ) ) );
 	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
-	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices ) );
+	// + the 8-byte overflow counter of the slot binning, cleared together with the counters
+	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) ) );
+	CKC( cudaMalloc( &b.bucket_slots, sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * (size_t)g.nt_pad * g.n_slices ) );
 	CKC( cudaMalloc( &b.bucket_off, sizeof( unsigned ) * ( n_buckets + 4 ) ) );
 	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( n_buckets / 1024 + 16 ) ) );
 	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );
@@ -937,12 +939,12 @@ static int enqueue_iteration( gs2d_ctx* c )
 	PROF( 0 );
 	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr );
 	PROF( 2 );
-	if( gs2d_pdl_usable( c->count_live ) )
+	if( gs2d_pdl_usable() )
 	{
 		// forward -> backward overlap (gs2d_blend.cuh): the two grids must be adjacent on the stream, so the loss is
 		// finalised behind the backward pass and profiling group 2 (forward) is empty, group 3 holds both passes
 		PROF( 3 );
-		c->launches += launch_forward( c->g, c->b, c->sorted_buf, false, s, true );
+		c->launches += launch_forward( c->g, c->b, c->sorted_buf, c->count_live, s, true );
 		c->launches += launch_backward( c->g, c->b, c->sorted_buf, c->hp.optimize_opacity != 0, false, s, true );
 		c->launches += launch_finalize_loss( c->g, c->b, s );
 	}

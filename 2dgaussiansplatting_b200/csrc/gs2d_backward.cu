@@ -397,10 +397,10 @@ void prepare_backward_pdl()
 	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
 }
 
-// PDL twins exist for the default register caps with the work counters off
-bool gs2d_pdl_usable( bool count_live )
+// PDL twins exist for the default register caps
+bool gs2d_pdl_usable()
 {
-	return gs2d_tune( "GS2D_PDL", 0 ) != 0 && !count_live &&
+	return gs2d_tune( "GS2D_PDL", 0 ) != 0 &&
 	       gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) == GS2D_FWD_MINB_DEFAULT &&
 	       gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT ) == GS2D_BWD_MINB_DEFAULT;
 }

@@ -88,13 +88,21 @@ struct PairOut
 {
 	unsigned long long* triple;  // bucket | local << 32 | rank << 48
 	unsigned long long* cnt64;   // [n_slices][nt_pad / 4] words of four 16-bit bucket counters (consecutive tiles)
+	// slot binning (GS2D_SLOTS, the default): the first GS2D_BUCKET_SLOTS arrivals of a bucket store their 16-bit index
+	// inside the slice straight into the bucket's own 16-byte slot row, [n_slices][nt_pad][GS2D_BUCKET_SLOTS]; only later
+	// arrivals (rare: 3.3 entries per bucket on average) become triples, appended at *n_over, and go through k_place
+	unsigned short* slots;
+	unsigned long long* n_over;
 };
 
 // Emit the pairs of tiles id_lo..id_hi (one tile row of one splat) at pos.., one 64-bit atomic per 4-tile group.
+template <bool SLOTS>
 __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
-                                          int slice, unsigned local, unsigned long long pos )
+                                          int slice, unsigned local, unsigned long long pos,
+                                          unsigned long long capacity )
 {
 	unsigned long long* cnt = o.cnt64 + (size_t)slice * ( g.nt_pad >> 2 );
+	unsigned short* slot_row = o.slots + (size_t)slice * g.nt_pad * GS2D_BUCKET_SLOTS;
 	for( unsigned grp = id_lo >> 2; grp <= ( id_hi >> 2 ); grp++ )
 	{
 		const unsigned f0 = max( id_lo, grp * 4u ) - grp * 4u, f1 = min( id_hi, grp * 4u + 3u ) - grp * 4u;
@@ -103,13 +111,25 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 		const unsigned long long old = atomicAdd( cnt + grp, add );
 		for( unsigned f = f0; f <= f1; f++, pos++ )
 		{
-			const unsigned bucket = ( grp * 4u + f ) * (unsigned)g.n_slices + (unsigned)slice;
+			const unsigned tile = grp * 4u + f;
+			const unsigned bucket = tile * (unsigned)g.n_slices + (unsigned)slice;
 			const unsigned long long rank = ( old >> ( 16u * f ) ) & 0xffffull;
-			__stcs( o.triple + pos, (unsigned long long)bucket | ( (unsigned long long)local << 32 ) | ( rank << 48 ) );
+			const unsigned long long t = (unsigned long long)bucket | ( (unsigned long long)local << 32 ) | ( rank << 48 );
+			if( !SLOTS )
+				__stcs( o.triple + pos, t );
+			else if( rank < (unsigned long long)GS2D_BUCKET_SLOTS )
+				slot_row[(size_t)tile * GS2D_BUCKET_SLOTS + (unsigned)rank] = (unsigned short)local;
+			else
+			{
+				const unsigned long long at = atomicAdd( o.n_over, 1ull );
+				if( at < capacity ) // cannot fail: the chunk's pairs were reserved against the capacity
+					__stcs( o.triple + at, t );
+			}
 		}
 	}
 }
 
+template <bool SLOTS>
 __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const float* __restrict__ params,
                                                                SplatRec* __restrict__ rec, PairOut out,
                                                                unsigned long long capacity, int cull,
@@ -310,7 +330,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 				const int ty = o.ty0 + (int)( item - first );
 				const unsigned lo = span & 0xfffu, hi = ( span >> 12 ) & 0xfffu;
 				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-				emit_row( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos );
+				emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
 				pos += hi - lo + 1u;
 			}
 		}
@@ -437,11 +457,12 @@ __device__ __forceinline__ unsigned splat_of_triple( const Geometry& g, unsigned
 __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned long long* __restrict__ triple,
                                                   const unsigned* __restrict__ offset,
                                                   const unsigned* __restrict__ sums, unsigned base,
-                                                  unsigned* __restrict__ list, const DevState* __restrict__ st )
+                                                  unsigned* __restrict__ list, const DevState* __restrict__ st,
+                                                  const unsigned long long* __restrict__ n_triples )
 {
 	if( st->need_capacity )
 		return;
-	const unsigned long long n = st->n_keys;
+	const unsigned long long n = *n_triples; // all pairs (st->n_keys) or, with slot binning, the overflow arrivals
 	const unsigned long long stride = (unsigned long long)gridDim.x * 256;
 	const unsigned tpi = (unsigned)( g.tiles_x * g.tiles_y );
 	unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x;
@@ -470,12 +491,16 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
 }
 
 // One thread per bucket: order its entries by splat index (rank by counting: the indices are unique), list -> out.
+// SLOTS: the first GS2D_BUCKET_SLOTS entries come from the bucket's slot row (16-bit indices inside the slice, one
+// 16-byte load), later arrivals from list[start + GS2D_BUCKET_SLOTS ..) where k_place put them.
+template <bool SLOTS>
 __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned short* __restrict__ cnt16,
                                                  const unsigned* __restrict__ offset,
                                                  const unsigned* __restrict__ sums,
-                                                 const unsigned* __restrict__ list, unsigned* __restrict__ out,
+                                                 unsigned* __restrict__ list, unsigned* __restrict__ out,
                                                  uint2* __restrict__ tile_range, unsigned base, unsigned n_buckets,
-                                                 const DevState* __restrict__ st )
+                                                 const DevState* __restrict__ st,
+                                                 const unsigned short* __restrict__ slots )
 {
 	if( st->need_capacity )
 		return;
@@ -489,8 +514,32 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		tile_range[tile].x = start;
 	if( slice == (unsigned)g.n_slices - 1 )
 		tile_range[tile].y = start + n;
-	const unsigned* p = list + start;
+	unsigned* p = list + start;
 	unsigned* q = out + start;
+	unsigned sl[GS2D_BUCKET_SLOTS];
+	if( SLOTS )
+	{
+		static_assert( GS2D_BUCKET_SLOTS == 8, "k_rank reads a slot row as one uint4 and sorts 8 registers" );
+		if( n == 0u )
+			return;
+		const uint4 w = __ldcs( reinterpret_cast<const uint4*>( slots + ( (size_t)slice * g.nt_pad + tile ) * GS2D_BUCKET_SLOTS ) );
+		// all entries of a bucket share the image and the slice: global index = first + index inside the slice
+		const unsigned first = ( tile / (unsigned)( g.tiles_x * g.tiles_y ) ) * (unsigned)g.n_splats + slice * (unsigned)g.slice_size;
+		sl[0] = first + ( w.x & 0xffffu );
+		sl[1] = first + ( w.x >> 16 );
+		sl[2] = first + ( w.y & 0xffffu );
+		sl[3] = first + ( w.y >> 16 );
+		sl[4] = first + ( w.z & 0xffffu );
+		sl[5] = first + ( w.z >> 16 );
+		sl[6] = first + ( w.w & 0xffffu );
+		sl[7] = first + ( w.w >> 16 );
+		if( n > 8u ) // rare: join the slot entries with the overflow arrivals in the unordered list, then rank below
+		{
+#pragma unroll
+			for( int a = 0; a < 8; a++ )
+				p[a] = sl[a];
+		}
+	}
 	if( n <= 8u )
 	{
 		// the common case (3.3 entries on average): a fixed 19-comparator network over 8 registers padded with
@@ -498,7 +547,7 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		unsigned e[8];
 #pragma unroll
 		for( int a = 0; a < 8; a++ )
-			e[a] = (unsigned)a < n ? p[a] : 0xffffffffu;
+			e[a] = (unsigned)a < n ? ( SLOTS ? sl[a] : p[a] ) : 0xffffffffu;
 #define CE( x, y )                                                                                                    \
 	{                                                                                                                 \
 		const unsigned lo_ = min( e[x], e[y] ), hi_ = max( e[x], e[y] );                                              \
@@ -544,12 +593,19 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		return 0;
 	}
 	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
-	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices, s );
+	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ), s );
+	const bool slots = gs2d_tune( "GS2D_SLOTS", 1 ) != 0;
 	PairOut po;
 	po.triple = b.triples;
 	po.cnt64 = reinterpret_cast<unsigned long long*>( b.bucket_cnt );
+	po.slots = b.bucket_slots;
+	// the overflow counter sits behind the bucket counters and is cleared with them
+	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + (size_t)g.nt_pad * g.n_slices );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
-	k_preprocess<<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
+	if( slots )
+		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
+	else
+		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
@@ -565,9 +621,20 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
 	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, lo, hi, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
-	k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state );
-	k_rank<<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1], b.vals[0],
-	                                               b.tile_range, lo, hi, b.state );
+	if( slots )
+	{
+		// few triples, if any: a small grid (the kernel is a grid-stride loop over *n_over)
+		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over );
+		k_rank<true><<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1],
+		                                                     b.vals[0], b.tile_range, lo, hi, b.state, b.bucket_slots );
+	}
+	else
+	{
+		k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state,
+		                                  &b.state->n_keys );
+		k_rank<false><<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1],
+		                                                      b.vals[0], b.tile_range, lo, hi, b.state, nullptr );
+	}
 	launches += 4;
 	return launches;
 }

@@ -225,6 +225,8 @@ void prepare_forward_pdl()
 {
 	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
 	                      cudaSharedmemCarveoutMaxShared );
+	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+	                      cudaSharedmemCarveoutMaxShared );
 }
 
 int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s, bool pdl )
@@ -235,13 +237,19 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 		return 0;
 	dim3 grid( g.tiles_x, rows, g.n_images );
 	const int vh = gs2d_tune( "GS2D_VISIT_HIST", 0 );
-	if( pdl ) // only the default variant (32 warps per SM, counters off) has a PDL twin: gs2d_pdl_usable()
+	if( pdl ) // only the default register cap (32 warps per SM) has PDL twins: gs2d_pdl_usable()
 	{
 		cudaMemsetAsync( b.tile_done, 0, sizeof( unsigned ) * (size_t)g.n_tiles_total, s );
-		k_forward<GS2D_FWD_MINB_DEFAULT, false, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
-		                                                                    b.target, b.image, b.cover, b.loss_partial,
-		                                                                    b.live_slots, b.staged_slots, b.state, 0,
-		                                                                    b.tile_done );
+		if( count_live )
+			k_forward<GS2D_FWD_MINB_DEFAULT, true, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
+			                                                                   b.target, b.image, b.cover, b.loss_partial,
+			                                                                   b.live_slots, b.staged_slots, b.state, vh,
+			                                                                   b.tile_done );
+		else
+			k_forward<GS2D_FWD_MINB_DEFAULT, false, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
+			                                                                    b.target, b.image, b.cover, b.loss_partial,
+			                                                                    b.live_slots, b.staged_slots, b.state, 0,
+			                                                                    b.tile_done );
 		return 1;
 	}
 #define LAUNCH_FWD( MINB )                                                                                            \

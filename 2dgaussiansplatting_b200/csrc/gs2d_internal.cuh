@@ -19,6 +19,7 @@
 #define GS2D_TILE 16          // tile edge in pixels; one warp per tile, 8 pixels per lane (gs2d_blend.cuh)
 #define GS2D_BATCH 32         // list entries staged into shared memory per round
 #define GS2D_NPLANES 9
+#define GS2D_BUCKET_SLOTS 8   // direct slots per (tile, index slice) bucket, 16-bit entries (gs2d_binning.cu)
 #define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
 #define GS2D_FWD_MINB_DEFAULT 32 // resident warps per SM the forward blend is register-capped for (env GS2D_FWD_MINB)
 #define GS2D_BWD_MINB_DEFAULT 24 // same for the backward blend (env GS2D_BWD_MINB)
@@ -159,6 +160,7 @@ struct Buffers
 	float* adam_v;  // [9][n_pad]
 	SplatRec* rec;  // [n_total]
 	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
+	unsigned short* bucket_slots; // [n_slices][nt_pad][GS2D_BUCKET_SLOTS] first arrivals of every bucket (slot binning)
 	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
 	unsigned* scan_sums;        // scratch of the scan
 	unsigned long long* triples; // [capacity] unordered (bucket, splat-in-slice, arrival rank) words, gs2d_binning.cu
@@ -186,12 +188,12 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 // developer tuning knob: integer environment variable read once per name, else the default
 int gs2d_tune( const char* env_name, int dflt );
 // pdl: forward/backward overlap through programmatic dependent launch (gs2d_blend.cuh); must be set for both or none,
-// backward directly behind forward on the stream, work counters off, default register caps (gs2d_pdl_usable)
+// backward directly behind forward on the stream, default register caps (gs2d_pdl_usable)
 int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s,
                     bool pdl = false );
 int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity, bool count_live,
                      cudaStream_t s, bool pdl = false );
-bool gs2d_pdl_usable( bool count_live );
+bool gs2d_pdl_usable();
 void prepare_forward_pdl();  // per-device kernel attributes of the PDL twins (called once by gs2d_create)
 void prepare_backward_pdl();
 int launch_finalize_loss( const Geometry& g, const Buffers& b, cudaStream_t s );
