@@ -400,7 +400,7 @@ void prepare_backward_pdl()
 // PDL twins exist for the default register caps
 bool gs2d_pdl_usable()
 {
-	return gs2d_tune( "GS2D_PDL", 0 ) != 0 &&
+	return gs2d_tune( "GS2D_PDL", 1 ) != 0 &&
 	       gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) == GS2D_FWD_MINB_DEFAULT &&
 	       gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT ) == GS2D_BWD_MINB_DEFAULT;
 }

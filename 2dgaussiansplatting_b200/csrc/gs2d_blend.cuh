@@ -51,7 +51,7 @@ __device__ __forceinline__ f32x2 xmul2( f32x2 a, f32x2 b )
 	return r;
 }
 
-// ---- forward -> backward overlap through programmatic dependent launch (opt-in: GS2D_PDL=1) -----------------------
+// ---- forward -> backward overlap through programmatic dependent launch (default; GS2D_PDL=0 turns it off) -----------------------
 // The blend grids end in a tail: one warp per tile, so the last resident tiles keep their SMs mostly idle for one
 // tile's run time (~50 us; twice per iteration, a quarter of a rank's blend time at N = 8). The backward pass of a
 // tile needs the forward pass of THAT tile only (its final pixels, coverage words), so in this mode

@@ -20,7 +20,7 @@
 // per 8x4 block visit, and of the live pixels left in the tile at each visit
 __device__ unsigned long long g_visit_hist[2][33];
 
-// PDL (GS2D_PDL=1, gs2d_blend.cuh): the backward grid is launched with programmatic stream serialization and fills the
+// PDL (default, GS2D_PDL=0 turns it off; gs2d_blend.cuh): the backward grid is launched with programmatic stream serialization and fills the
 // SM slots the forward pass's last wave frees; a tile's forward warp publishes tile_done[tile] when its image pixels,
 // coverage words and loss partial are written, and the tile's backward warp waits for exactly that.
 template <int MINB, bool COUNT, bool PDL>

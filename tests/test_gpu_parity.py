@@ -228,6 +228,60 @@ def test_ellipse_culling_is_a_superset_of_the_footprint():
         assert st1["keys"] < st0["keys"]
 
 
+def test_slot_binning_equals_the_triple_path():
+    """Slot binning (first 8 arrivals of a (tile, slice) bucket stored straight into the bucket's slot row, the rest
+    through k_place) must build the same ordered lists as the triple path: bit-identical images, same live pairs and
+    list entries - also with hundreds of entries per bucket (every bucket overflows its slot row)."""
+    W, H = 700, 520
+    rng = np.random.default_rng(21)
+    cases = [random_splats(rng, W, H, 6000, smin=2, smax=14), random_splats(rng, W, H, 1500, smin=100, smax=900,
+                                                                          opacity=(0.1, 0.3))]
+    for splats in cases:
+        out = []
+        for slots in (0, 1):
+            gs2d.set_tuning("GS2D_SLOTS", slots)
+            try:
+                with gs2d.Fitter(W, H, len(splats)) as fit:
+                    fit.set_target(gs2d.synth_target(W, H, seed=3))
+                    fit.upload(splats)
+                    fit.forward()
+                    out.append((fit.image(), fit.stats()))
+            finally:
+                gs2d.set_tuning("GS2D_SLOTS", 1)
+        (img0, st0), (img1, st1) = out
+        assert img0.tobytes() == img1.tobytes()
+        assert st0["live_pairs"] == st1["live_pairs"] and st0["keys"] == st1["keys"]
+
+
+def test_forward_backward_overlap_equals_the_serialised_launch():
+    """gs2d_step launches the backward grid inside the forward grid's tail (programmatic dependent launch + per-tile
+    flags, gs2d_blend.cuh). The fit must not depend on it: first loss bit-identical, the curve within the noise of the
+    unordered gradient atomics, with the work counters on and off, replayed as a graph and as plain launches."""
+    W, H, n = 1024, 768, 60000
+    target = gs2d.synth_target(W, H, seed=5)
+    runs = {}
+    try:
+        for pdl in (0, 1):
+            for stats in (True, False):
+                for graph in (1, 0):
+                    gs2d.set_tuning("GS2D_PDL", pdl)
+                    gs2d.set_tuning("GS2D_GRAPH", graph)
+                    with gs2d.Fitter(W, H, n) as fit:
+                        fit.set_target(target)
+                        fit.set_stats(stats)
+                        fit.restart()
+                        mse = fit.step(12)[:, 0]
+                        runs[(pdl, stats, graph)] = (mse, fit.image())
+    finally:
+        gs2d.set_tuning("GS2D_PDL", 1)
+        gs2d.set_tuning("GS2D_GRAPH", 1)
+    ref_mse, _ = runs[(0, True, 0)]
+    for key, (mse, img) in runs.items():
+        assert mse[0] == ref_mse[0], key
+        assert np.max(np.abs(mse - ref_mse) / ref_mse) < 1e-6, key
+        assert np.isfinite(img).all() and (img[..., 3] == 1.0).all(), key
+
+
 def test_nonfinite_is_reported_not_aborted():
     W, H = 64, 64
     s = ob.init_splats(W, H, 8)
