@@ -179,12 +179,17 @@ int gs2d_last_step_ms( gs2d_ctx* ctx, float* ms );
 int gs2d_profile_step( gs2d_ctx* ctx, float out_ms[6] );
 /* Continuous profiling: while enabled, every iteration enqueued by gs2d_step is bracketed by CUDA events on the
  * context's stream; gs2d_get_profile waits for the stream and returns the summed device time of each kernel group
- * (same order as gs2d_profile_step) and the number of iterations measured. gs2d_set_profiling resets the sums. */
+ * (same order as gs2d_profile_step) and the number of iterations measured. gs2d_set_profiling resets the sums.
+ * With the forward -> backward overlap on (the default, see GS2D_PDL below) the two blend grids run concurrently and
+ * only the pair can be bracketed: group 2 (forward) then holds two memsets and group 3 (backward) both passes. */
 int gs2d_set_profiling( gs2d_ctx* ctx, int enable );
 int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
 /* Developer knobs (process-wide; same names as the environment variables they override): "GS2D_CULL" 0/1 = bin
  * with the conservative tile rectangle only / with the per-tile-row ellipse spans (default; same images, fewer keys),
- * "GS2D_FWD_MINB" 32/24/20 and "GS2D_BWD_MINB" 20/16 = register caps of the blend kernels. */
+ * "GS2D_FWD_MINB" 32/24/20 and "GS2D_BWD_MINB" 24/20/16 = register caps of the blend kernels,
+ * "GS2D_SLOTS" 1/0 = slot binning (default) / every (tile, Gaussian) pair through the place pass (same lists),
+ * "GS2D_PDL" 1/0 = backward grid launched inside the forward grid's tail (default; needs the default register
+ * caps) / the two grids serialised (same results), "GS2D_GRAPH" 1/0 = iterations replayed as a CUDA graph. */
 int gs2d_set_tuning( const char* name, int value );
 /* Work counters on/off (default on): while off, the forward blend launched by gs2d_step does not count live pairs
  * (one instruction per 8x4 block visit); gs2d_forward / gs2d_backward always count. */
