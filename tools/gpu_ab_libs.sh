@@ -1,6 +1,10 @@
 #!/bin/bash
 # compile-time A/B on one box: the same variant list against libgs2d_base.so (previous commit) and libgs2d.so,
-# then (optionally) the GPU test suite against the new library
+# then (optionally) the GPU test suite against the new library. Boxes differ by +-1.5 %, so only numbers of ONE call
+# compare. Build the base first (it travels with the snapshot, *.so is git-ignored):
+#   rm -rf /tmp/base && mkdir /tmp/base && git archive HEAD | tar -x -C /tmp/base && \
+#   make -C /tmp/base/2dgaussiansplatting_b200/csrc -j8 && \
+#   cp /tmp/base/2dgaussiansplatting_b200/libgs2d.so 2dgaussiansplatting_b200/libgs2d_base.so
 # usage: gpurun -- 'bash tools/gpu_ab_libs.sh TAG REPS pytest|nopytest VARIANT...'
 OUT=gpurun_out; mkdir -p $OUT; TAG=${1:-ablib}; REPS=${2:-1}; PYT=${3:-nopytest}; shift 3
 show() { python -c "
