@@ -114,6 +114,14 @@ struct gs2d_ctx
 	void* dstage = nullptr; // device staging (AoS <-> SoA, u8 targets)
 	size_t dstage_bytes = 0;
 	DevState* h_state = nullptr; // pinned mirror
+	// Slot binning (gs2d_binning.cu) is built for buckets of a few entries; when Gaussians have grown so large that most
+	// arrivals overflow their bucket's slot row, every overflow costs an atomic on ONE counter and the triple path
+	// (one reservation per warp chunk) is the faster one. Both build identical lists, so the context simply switches
+	// at its synchronisation points: off when more than a quarter of the last iteration's pairs overflowed, on again
+	// (to look) 256 iterations later.
+	bool slot_binning = true;
+	long long slot_retry_at = 0;
+	unsigned long long* h_n_over = nullptr; // pinned: overflow arrivals of the last iteration
 
 	// asynchronous target upload (gs2d_set_target_rgba8_async): H2D on its own stream into one of two device staging
 	// buffers; the u8 -> float conversion is enqueued on the main stream by the next forward (apply_pending_target)
@@ -376,6 +384,8 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 		cudaFreeHost( c->pinned );
 	if( c->h_state )
 		cudaFreeHost( c->h_state );
+	if( c->h_n_over )
+		cudaFreeHost( c->h_n_over );
 	for( auto& e : c->ev )
 		if( e )
 			cudaEventDestroy( e );
@@ -490,6 +500,8 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.mse_ring, sizeof( double ) * (size_t)b.mse_cap * n_images ) );
 	CKC( cudaMalloc( &b.state, sizeof( DevState ) ) );
 	CKC( cudaMallocHost( &c->h_state, sizeof( DevState ) ) );
+	CKC( cudaMallocHost( &c->h_n_over, sizeof( unsigned long long ) ) );
+	*c->h_n_over = 0;
 	CKC( cudaMemset( b.params, 0, plane_bytes ) );
 	CKC( cudaMemset( b.grads, 0, plane_bytes ) );
 	CKC( cudaMemset( b.adam_m, 0, plane_bytes ) );
@@ -714,8 +726,31 @@ extern "C" int gs2d_upload_state( gs2d_ctx* c, int image, const gs2d_splat* spla
 static int fetch_state( gs2d_ctx* c )
 {
 	CK( cudaMemcpyAsync( c->h_state, c->b.state, sizeof( DevState ), cudaMemcpyDeviceToHost, c->stream ) );
+	// the overflow counter of the slot binning sits behind the bucket counters (launch_preprocess_and_bin)
+	CK( cudaMemcpyAsync( c->h_n_over, c->b.bucket_cnt + (size_t)c->g.nt_pad * c->g.n_slices, sizeof( unsigned long long ),
+	                     cudaMemcpyDeviceToHost, c->stream ) );
 	CK( cudaStreamSynchronize( c->stream ) );
 	return GS2D_OK;
+}
+
+// see gs2d_ctx::slot_binning; called with a fresh h_state / h_n_over and nothing in flight
+static void adapt_binning( gs2d_ctx* c )
+{
+	const DevState& s = *c->h_state;
+	const bool was = c->slot_binning;
+	if( c->slot_binning )
+	{
+		if( s.need_capacity == 0 && s.n_keys > 0 && *c->h_n_over * 4ull > s.n_keys )
+		{
+			c->slot_binning = false;
+			c->slot_retry_at = c->expected_iteration + 256;
+		}
+	}
+	else if( c->expected_iteration >= c->slot_retry_at )
+		c->slot_binning = true;
+	if( was != c->slot_binning && gs2d_tune( "GS2D_DEBUG_BINNING", 0 ) )
+		fprintf( stderr, "[gs2d] slot binning %s at iteration %lld (%llu of %llu pairs overflowed their slot row)\n",
+		         c->slot_binning ? "on" : "off", c->expected_iteration, *c->h_n_over, s.n_keys );
 }
 
 static int download_aos( gs2d_ctx* c, int image, gs2d_splat* splats, gs2d_splat_adam* adam, gs2d_splat* grads )
@@ -824,7 +859,7 @@ static int enqueue_forward( gs2d_ctx* c )
 	int rcp = apply_pending_target( c );
 	if( rcp )
 		return rcp;
-	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr, c->slot_binning );
 	c->launches += launch_forward( c->g, c->b, c->sorted_buf, true, c->stream );
 	c->launches += launch_finalize_loss( c->g, c->b, c->stream );
 	c->have_forward = true;
@@ -937,7 +972,7 @@ static int enqueue_iteration( gs2d_ctx* c )
 	if( pr )                                                                                                          \
 	cudaEventRecord( pr->ev[i], s )
 	PROF( 0 );
-	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr, c->slot_binning );
 	PROF( 2 );
 	if( gs2d_pdl_usable() )
 	{
@@ -989,6 +1024,7 @@ static int enqueue_iterations( gs2d_ctx* c, int n )
 		key.mse_cap = c->b.mse_cap;
 		key.count_live = c->count_live ? 1 : 0;
 		key.tune_epoch = g_tune_epoch;
+		key.pad = c->slot_binning ? 1 : 0;
 		if( !c->iter_graph || memcmp( &key, &c->graph_key, sizeof( key ) ) != 0 )
 		{
 			if( c->iter_graph )
@@ -1072,6 +1108,7 @@ static int resolve( gs2d_ctx* c )
 		const long long missing = c->expected_iteration - (long long)s.iteration;
 		if( s.need_capacity == 0 && missing <= 0 )
 		{
+			adapt_binning( c );
 			collect_profile( c );
 			return s.nonfinite ? GS2D_ERR_NONFINITE : GS2D_OK;
 		}

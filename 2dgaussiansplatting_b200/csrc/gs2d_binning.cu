@@ -580,7 +580,7 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 
 // ---------------------------------------------------------------------------------------------------- launch ---
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
-                               cudaEvent_t after_emit )
+                               cudaEvent_t after_emit, bool use_slots )
 {
 	int launches = 0;
 	*sorted_buf = 0; // the ordered lists end up in vals[0]
@@ -594,7 +594,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	}
 	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
 	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ), s );
-	const bool slots = gs2d_tune( "GS2D_SLOTS", 1 ) != 0;
+	const bool slots = use_slots && gs2d_tune( "GS2D_SLOTS", 1 ) != 0;
 	PairOut po;
 	po.triple = b.triples;
 	po.cnt64 = reinterpret_cast<unsigned long long*>( b.bucket_cnt );

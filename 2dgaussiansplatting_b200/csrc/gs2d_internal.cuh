@@ -183,8 +183,9 @@ struct Buffers
 
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
+// use_slots: slot binning unless the context has switched it off for now (gs2d_ctx::slot_binning) or GS2D_SLOTS=0
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
-                               cudaEvent_t after_emit );
+                               cudaEvent_t after_emit, bool use_slots );
 // developer tuning knob: integer environment variable read once per name, else the default
 int gs2d_tune( const char* env_name, int dflt );
 // pdl: forward/backward overlap through programmatic dependent launch (gs2d_blend.cuh); must be set for both or none,

@@ -253,6 +253,20 @@ def test_slot_binning_equals_the_triple_path():
         assert st0["live_pairs"] == st1["live_pairs"] and st0["keys"] == st1["keys"]
 
 
+def test_binning_switches_paths_when_slot_rows_overflow():
+    """A context whose Gaussians overflow nearly every slot row switches to the triple path at its first
+    synchronisation point (one atomic per overflow arrival on a single counter is the slow case of slot binning) and
+    must give the same loss curve as GS2D_SLOTS=0; a normal fit stays on the slot path. tools/adapt_check.py."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "adapt_check.py")], capture_output=True, text=True,
+                       timeout=300, env=dict(os.environ, GS2D_DEBUG_BINNING="1"))
+    assert r.returncode == 0 and "adapt_check OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "slot binning off at iteration 1" in r.stderr, r.stderr[-2000:]
+
+
 def test_forward_backward_overlap_equals_the_serialised_launch():
     """gs2d_step launches the backward grid inside the forward grid's tail (programmatic dependent launch + per-tile
     flags, gs2d_blend.cuh). The fit must not depend on it: first loss bit-identical, the curve within the noise of the
