@@ -191,7 +191,7 @@ struct gs2d_ctx
 	std::vector<ProfRec> prof_pool;
 	size_t prof_used = 0;
 	bool profiling = false;
-	bool count_live = true;              // gs2d_set_stats: count live pairs / staged entries in the forward blend
+	bool count_live = false;             // gs2d_set_stats: count live pairs / staged entries in the forward blend of gs2d_step
 	unsigned long long bwd_live = 0;     // live pairs counted by the last gs2d_backward
 	double prof_sum[6] = { 0, 0, 0, 0, 0, 0 };
 	long long prof_iters = 0;

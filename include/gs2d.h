@@ -191,7 +191,7 @@ int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
  * "GS2D_PDL" 1/0 = backward grid launched inside the forward grid's tail (default; needs the default register
  * caps) / the two grids serialised (same results), "GS2D_GRAPH" 1/0 = iterations replayed as a CUDA graph. */
 int gs2d_set_tuning( const char* name, int value );
-/* Work counters on/off (default on): while off, the forward blend launched by gs2d_step does not count live pairs
+/* Work counters on/off (default off): while off, the forward blend launched by gs2d_step does not count live pairs
  * (one instruction per 8x4 block visit); gs2d_forward / gs2d_backward always count. */
 int gs2d_set_stats( gs2d_ctx* ctx, int enable );
 /* Number of kernel launches the library has issued on this context so far. */
