@@ -1102,7 +1102,12 @@ static int resolve( gs2d_ctx* c )
 		const DevState& s = *c->h_state;
 		if( s.peer_fault )
 		{
-			snprintf( c->err, sizeof( c->err ), s.peer_fault == 2 ? "a forward -> backward tile flag did not arrive (GS2D_PDL)" : "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
+			if( s.peer_fault == 2 )
+			{
+				snprintf( c->err, sizeof( c->err ), "a forward -> backward tile flag did not arrive within its time-out (GS2D_PDL=0 serialises the two blend grids)" );
+				return GS2D_ERR_CUDA;
+			}
+			snprintf( c->err, sizeof( c->err ), "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
 			return GS2D_ERR_NCCL;
 		}
 		const long long missing = c->expected_iteration - (long long)s.iteration;
