@@ -24,50 +24,6 @@
 
 #define PRE_THREADS 256
 
-// Conservative column span [tx_lo, tx_hi] of the tiles of tile row ty that the splat's footprint can touch.
-// The reference covers pixel (x, y) iff begY <= y <= endY and x in [(int)(px+u0), (int)(px+u1)], u0/u1 the chord of the
-// ellipse q(v) = a vx^2 + 2 b vx vy + d vy^2 <= 9 at the row centre vy = y + 0.5 - py (main.cpp:489-509). (int)
-// moves an end by less than one pixel, so a tile [X0, X0+16) can only be touched if the x-extent [min u0, max u1] of
-// the ellipse inside the band of this tile row's pixel centres reaches (X0 - 1, X0 + 16). The ellipse is convex:
-// max u1 over the band is the ellipse's rightmost point if that lies in the band, else it is at a band end.
-// Returns false if no row of the tile row is inside [begY, endY].
-struct SpanConsts
-{
-	float px, py, a, b, d;
-	float inv_a;    // 1 / a
-	float vx_max;   // 3 * sqrt( d / (a d - b^2) ): half width of the ellipse
-	float vy_at;    // vy of the rightmost point: -b * vx_max / d   (leftmost: -vy_at)
-	float delta;    // slack for float error of everything here and of the reference's own float chord solve
-	int begY, endY;
-};
-
-__device__ __forceinline__ bool tile_span( const SpanConsts& k, int ty, int H, int rtx0, int rtx1, int& tx_lo,
-                                           int& tx_hi )
-{
-	const int Y0 = ty * GS2D_TILE;
-	const int ylo = max( max( Y0, k.begY ), 0 ), yhi = min( min( Y0 + GS2D_TILE - 1, k.endY ), H - 1 );
-	if( ylo > yhi )
-		return false;
-	const float lo = ( (float)ylo + 0.5f - k.py ) - k.delta, hi = ( (float)yhi + 0.5f - k.py ) + k.delta;
-	// chord ends at the two band ends
-	const float bl = k.b * lo, bh = k.b * hi;
-	const float sl = sqrtf( fmaxf( bl * bl - k.a * ( k.d * lo * lo - 9.0f ), 0.0f ) );
-	const float sh = sqrtf( fmaxf( bh * bh - k.a * ( k.d * hi * hi - 9.0f ), 0.0f ) );
-	float umax = fmaxf( ( -bl + sl ) * k.inv_a, ( -bh + sh ) * k.inv_a );
-	float umin = fminf( ( -bl - sl ) * k.inv_a, ( -bh - sh ) * k.inv_a );
-	if( lo <= k.vy_at && k.vy_at <= hi )
-		umax = k.vx_max;
-	if( lo <= -k.vy_at && -k.vy_at <= hi )
-		umin = -k.vx_max;
-	const float E = k.px + umin - k.delta;         // a tile needs X0 + 16 > E
-	const float F = k.px + umax + 1.0f + k.delta;  // and X0 < F
-	// NaN anywhere -> fmaxf/fminf return the rectangle bound: the conservative rectangle is the fallback
-	tx_lo = (int)fmaxf( floorf( E * ( 1.0f / GS2D_TILE ) ), (float)rtx0 );
-	tx_hi = (int)fminf( floorf( F * ( 1.0f / GS2D_TILE ) ), (float)rtx1 );
-	return tx_lo <= tx_hi;
-}
-
-
 // ------------------------------------------------------------------------------------------------ preprocess ---
 // Per-splat part: record + span constants + conservative tile rectangle (tile units; empty if rtx0 > rtx1).
 struct SplatBin
@@ -169,21 +125,10 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			sincos( (double)rot, &sd, &cd );
 			const float c = (float)cd, s = (float)sd;
 
-			// cov_of, main.cpp:214-220
-			const float l0 = xmul( sx, sx );
-			const float l1 = xmul( sy, sy );
-			const float s11 = xadd( xmul( xmul( l0, c ), c ), xmul( xmul( l1, s ), s ) );
-			const float s12 = xmul( xmul( xsub( l0, l1 ), s ), c );
-			const float s22 = xsub( xadd( l0, l1 ), s11 );
-			const float det = xsub( xmul( s11, s22 ), xmul( s12, s12 ) ); // main.cpp:191, :560
-			// inv_cov = mat2( cov[1][1], -cov[0][1], -cov[1][0], cov[0][0] ) / det, main.cpp:432-436
-			const float a = xdiv( s22, det );
-			const float b = xdiv( -s12, det );
-			const float d = xdiv( s11, det );
-			// row range, main.cpp:489-491
-			const float h = xmul( xsqrt( xmul( a, det ) ), 3.0f );
-			const int begY = trunc_x86( xsub( py, h ) );
-			const int endY = trunc_x86( xadd( py, h ) );
+			// cov_of, its inverse and the row range (main.cpp:206-221, :432-436, :489-491): gs2d_footprint.cuh
+			const SplatGeom ge = splat_geometry( py, sx, sy, c, s );
+			const float det = ge.det, a = ge.a, b = ge.b, d = ge.d;
+			const int begY = ge.begY, endY = ge.endY;
 
 			SplatRec r;
 			r.px = px;
@@ -216,7 +161,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			// per-pixel set is decided by row_mask() in the forward blend.
 			const int H = g.H, W = g.W;
 			const int y0 = max( begY, 0 ), y1 = min( endY, H - 1 );
-			const float hx = xmul( xsqrt( xmul( d, det ) ), 3.0f );
+			const float hx = half_width_x( ge );
 			const float m = 2.0f + hx * 1.0e-4f;
 			const float fx0 = floorf( px - hx - m ), fx1 = floorf( px + hx + m );
 			const int x0 = ( fx0 == fx0 ) ? (int)fmaxf( fx0, 0.0f ) : 0;
@@ -242,7 +187,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			sb.k.inv_a = 1.0f / a;
 			sb.k.vx_max = hx; // 3 * sqrt( cov[0][0] ) == 3 * sqrt( d / (a d - b^2) )
 			sb.k.vy_at = -b * hx / d;
-			sb.k.delta = cull ? 0.02f + 1.0e-3f * hx + 1.0e-6f * fabsf( px ) : __int_as_float( 0x7fc00000 ); // NaN: no culling
+			sb.k.delta = span_delta( px, hx, cull );
 			sb.k.begY = begY;
 			sb.k.endY = endY;
 		}

@@ -77,62 +77,7 @@ struct Geometry
 	float min_throughput;    // MIN_THROUGHPUT, main.cpp:8
 };
 
-// ---------------------------------------------------------------------------------------------------------------
-// Contraction-free float helpers. The reference build never fuses a*b+c (MSVC /fp:precise), and the
-// footprint / transmittance decisions are step functions of rounded values, so everything that feeds a decision is
-// written with these (nvcc never contracts the _rn intrinsics).
-// ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float xmul( float a, float b ) { return __fmul_rn( a, b ); }
-__device__ __forceinline__ float xadd( float a, float b ) { return __fadd_rn( a, b ); }
-__device__ __forceinline__ float xsub( float a, float b ) { return __fsub_rn( a, b ); }
-__device__ __forceinline__ float xdiv( float a, float b ) { return __fdiv_rn( a, b ); }
-__device__ __forceinline__ float xsqrt( float a ) { return __fsqrt_rn( a ); }
-
-// (int)f as the reference's x86 build does it (cvttss2si): toward zero; NaN / out of range -> INT_MIN.
-__device__ __forceinline__ int trunc_x86( float f )
-{
-	return ( f > -2147483648.0f && f < 2147483648.0f ) ? __float2int_rz( f ) : (int)0x80000000;
-}
-
-// exp_approx( -0.5f * d2 ), main.cpp:49-83.  1 + (-0.5*d2)/8 == fma(d2, -1/16, 1) bit for bit (the two scalings are
-// exact powers of two, so both forms round once).
-__device__ __forceinline__ float gauss_of_d2( float d2 )
-{
-	float t = __fmaf_rn( d2, -0.0625f, 1.0f );
-	float t2 = xmul( t, t );
-	float t4 = xmul( t2, t2 );
-	float t8 = xmul( t4, t4 );
-	return ( t < 0.00001814586175896693021059036255f ) ? 0.0f : t8;
-}
-
-// 16-bit coverage mask of tile row y for one splat: bit x set <=> pixel (tile_x0 + x, y) is inside the reference's
-// scan-line footprint (main.cpp:492-514): y in [begY, endY], x in [(int)(pos.x+u0), (int)(pos.x+u1)] where u0,u1
-// are the roots returned by solve_quadratic (main.cpp:171-185), x and y inside the image.
-__device__ __forceinline__ unsigned row_mask( float px, float py, float a, float b, float d, int begY, int endY,
-                                              int y, int tile_x0, int W, int H )
-{
-	if( y < begY || y > endY || y >= H )
-		return 0u;
-	float vy = xsub( xadd( (float)y, 0.5f ), py );
-	float qb = xmul( xmul( 2.0f, b ), vy );                    // 2.0f * b * vy
-	float qc = xsub( xmul( xmul( d, vy ), vy ), 9.0f );        // d * vy * vy - SPLAT_BOUNDS * SPLAT_BOUNDS
-	float det = xsub( xmul( qb, qb ), xmul( xmul( 4.0f, a ), qc ) ); // b*b - 4.0f*a*c
-	if( det < 0.0f )
-		return 0u;
-	float sgn = qb < 0.0f ? -1.0f : 1.0f;
-	float k = xmul( xsub( -qb, xmul( sgn, xsqrt( det ) ) ), 0.5f ); // ( -b - sign_of(b)*sqrtf(det) ) / 2.0f
-	float x0 = xdiv( k, a );
-	float x1 = xdiv( qc, k );
-	float u0 = ( x1 < x0 ) ? x1 : x0; // ss_min( x0, x1 )
-	float u1 = ( x0 < x1 ) ? x1 : x0; // ss_max( x0, x1 )
-	int begX = trunc_x86( xadd( px, u0 ) );
-	int endX = trunc_x86( xadd( px, u1 ) );
-	int lo = max( begX, tile_x0 ) - tile_x0;
-	int hi = min( min( endX, tile_x0 + GS2D_TILE - 1 ), W - 1 ) - tile_x0;
-	if( lo > hi )
-		return 0u;
-	return ( ( 2u << hi ) - 1u ) & ~( ( 1u << lo ) - 1u );
-}
+#include "gs2d_footprint.cuh" // contraction-free helpers, exp_approx, exact row footprint, tile-row spans
 
 // ---------------------------------------------------------------------------------------------------------------
 // cp.async (LDGSTS) 16-byte gather into shared memory.
