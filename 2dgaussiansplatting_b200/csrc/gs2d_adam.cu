@@ -1,13 +1,7 @@
 // gs2d_adam.cu — loss finalisation, Adam + clamps (main.cpp:714-785), reference init (main.cpp:280-305) and the
 // AoS <-> SoA conversions at the ABI.
 #include "gs2d_internal.cuh"
-
-// glm::clamp = min( max( x, lo ), hi ) with comparison-based min/max (func_common.inl:17-30): NaN survives.
-__device__ __forceinline__ float clamp_glm( float x, float lo, float hi )
-{
-	float t = ( x < lo ) ? lo : x;
-	return ( hi < t ) ? hi : t;
-}
+#include "gs2d_update.cuh"
 
 // ------------------------------------------------------------------------------------------------------ loss ---
 // One block per image: deterministic sum of the per-tile partials of this rank's band (double).
@@ -85,19 +79,7 @@ __global__ void k_advance( Geometry g, const double* __restrict__ loss, double* 
 }
 
 // ------------------------------------------------------------------------------------------------------ Adam ---
-// Adam::optimize, main.cpp:144-156 — reference operand order, IEEE division and square root, no contraction.
-__device__ __forceinline__ float adam_one( float value, float gr, float& m_io, float& v_io, float lr, float beta1,
-                                           float beta2, float eps, float om_b1t, float om_b2t )
-{
-	const float m = xadd( xmul( beta1, m_io ), xmul( xsub( 1.0f, beta1 ), gr ) );
-	const float v = xadd( xmul( beta2, v_io ), xmul( xmul( xsub( 1.0f, beta2 ), gr ), gr ) );
-	m_io = m;
-	v_io = v;
-	const float m_hat = xdiv( m, om_b1t );
-	const float v_hat = xdiv( v, om_b2t );
-	return xsub( value, xdiv( xmul( lr, m_hat ), xadd( xsqrt( v_hat ), eps ) ) );
-}
-
+// adam_one, clamp_glm: gs2d_update.cuh
 // One thread per (plane, 4 consecutive splats) - blockIdx.y is the plane, the nine scalars of a splat are independent
 // in Adam (main.cpp:723-738) - 128-bit accesses on every SoA plane: reads p, g, m, v, writes p, m, v and zeroes g for the
 // next iteration (28 + 4 bytes per scalar; HBM-bound).
@@ -345,48 +327,17 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 }
 
 // ------------------------------------------------------------------------------------------------------ init ---
-__device__ __forceinline__ void pcg3d( unsigned& x, unsigned& y, unsigned& z ) // main.cpp:17-24
-{
-	x = x * 1664525u + 1013904223u;
-	y = y * 1664525u + 1013904223u;
-	z = z * 1664525u + 1013904223u;
-	x += y * z;
-	y += z * x;
-	z += x * y;
-	x ^= x >> 16u;
-	y ^= y >> 16u;
-	z ^= z >> 16u;
-	x += y * z;
-	y += z * x;
-	z += x * y;
-}
-__device__ __forceinline__ float mix_glm( float x, float y, float a ) // x*(1-a) + y*a, func_common.inl:123-133
-{
-	return xadd( xmul( x, xsub( 1.0f, a ) ), xmul( y, a ) );
-}
-
+// pcg3d, mix_glm, init_splat: gs2d_update.cuh
 __global__ void __launch_bounds__( 256 ) k_init_reference( Geometry g, float* __restrict__ params )
 {
 	const int gi = blockIdx.x * 256 + threadIdx.x;
 	if( gi >= g.n_total )
 		return;
-	const unsigned i = (unsigned)( gi % g.n_splats );
-	unsigned ax = i, ay = 0u, az = 0xFFFFFFFFu, bx = i, by = 1u, bz = 0xFFFFFFFFu;
-	pcg3d( ax, ay, az );
-	pcg3d( bx, by, bz );
-	const float denom = 4294967296.0f; // (float)0xFFFFFFFF, main.cpp:290-291
-	const float r0x = xdiv( __uint2float_rn( ax ), denom ), r0y = xdiv( __uint2float_rn( ay ), denom );
-	const float r1x = xdiv( __uint2float_rn( bx ), denom ), r1y = xdiv( __uint2float_rn( by ), denom ),
-	            r1z = xdiv( __uint2float_rn( bz ), denom );
-	params[PL_PX * g.n_pad + gi] = mix_glm( r0x, xsub( (float)g.W, 1.0f ), r0x );
-	params[PL_PY * g.n_pad + gi] = mix_glm( r0y, xsub( (float)g.H, 1.0f ), r0y );
-	params[PL_SX * g.n_pad + gi] = mix_glm( 6.0f, 10.0f, r1x );
-	params[PL_SY * g.n_pad + gi] = mix_glm( 6.0f, 10.0f, r1y );
-	params[PL_ROT * g.n_pad + gi] = xmul( 3.14159265358979323846264338327950288f, r1z );
-	params[PL_CR * g.n_pad + gi] = 0.5f;
-	params[PL_CG * g.n_pad + gi] = 0.5f;
-	params[PL_CB * g.n_pad + gi] = 0.5f;
-	params[PL_OP * g.n_pad + gi] = 1.0f;
+	float v[GS2D_NPLANES];
+	init_splat( (unsigned)( gi % g.n_splats ), g.W, g.H, v );
+#pragma unroll
+	for( int pl = 0; pl < GS2D_NPLANES; pl++ )
+		params[pl * g.n_pad + gi] = v[pl];
 }
 
 // Image2DRGBA8_to_Image2DRGBA32: vec4( u8 ) / vec4( 255.0f ), prp.cpp:796-807

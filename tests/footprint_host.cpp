@@ -6,30 +6,7 @@
 // binning emits). This file includes that very header with the CUDA rounding intrinsics mapped to plain IEEE float
 // operations (compile with -ffp-contract=off, like the reference build) and exports two C functions for
 // tests/test_footprint_host.py, which checks them against the CPU oracle without a GPU.
-#include <math.h>
-#include <stdint.h>
-#include <string.h>
-
-#include <algorithm>
-
-#define __device__
-#define __forceinline__ inline
-#define GS2D_TILE 16
-static inline float __fmul_rn( float a, float b ) { return a * b; }
-static inline float __fadd_rn( float a, float b ) { return a + b; }
-static inline float __fsub_rn( float a, float b ) { return a - b; }
-static inline float __fdiv_rn( float a, float b ) { return a / b; }
-static inline float __fsqrt_rn( float a ) { return sqrtf( a ); }
-static inline float __fmaf_rn( float a, float b, float c ) { return fmaf( a, b, c ); }
-static inline int __float2int_rz( float f ) { return (int)f; } // trunc_x86 has excluded NaN / out of range before
-static inline float __int_as_float( int i )
-{
-	float f;
-	memcpy( &f, &i, 4 );
-	return f;
-}
-using std::max;
-using std::min;
+#include "host_shim.h"
 
 #include "../2dgaussiansplatting_b200/csrc/gs2d_footprint.cuh"
 
