@@ -64,6 +64,14 @@ __global__ void k_advance( Geometry g, const double* __restrict__ loss, double* 
 {
 	if( loss[g.n_images] != 0.0 )
 		return; // some rank ran out of key capacity: the iteration is void everywhere (redone by the host)
+	if( st->nonfinite )
+	{
+		// the previous iteration's update produced a non-finite parameter: the reference has aborted (main.cpp:752-785);
+		// nothing advances any more (DevState::frozen)
+		if( threadIdx.x == 0 )
+			st->frozen = 1;
+		return;
+	}
 	const int slot = st->mse_slot;
 	for( int i = threadIdx.x; i < g.n_images; i += blockDim.x )
 		if( slot < mse_cap )
@@ -87,7 +95,7 @@ __global__ void __launch_bounds__( 256 ) k_adam( Geometry g, float* __restrict__
                                                  float* __restrict__ adam_m, float* __restrict__ adam_v,
                                                  gs2d_params hp, const double* __restrict__ loss, DevState* st )
 {
-	if( loss[g.n_images] != 0.0 )
+	if( loss[g.n_images] != 0.0 || st->frozen )
 		return;
 	const int i4 = ( blockIdx.x * 256 + threadIdx.x ) * 4;
 	if( i4 >= g.n_total )
@@ -243,7 +251,7 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
                                                       float* __restrict__ adam_v, gs2d_params hp,
                                                       const double* __restrict__ loss, DevState* st, int q0, int q1 )
 {
-	if( loss[g.n_images] != 0.0 )
+	if( loss[g.n_images] != 0.0 || st->frozen )
 		return;
 	const int q = q0 + blockIdx.x * 128 + threadIdx.x;
 	if( q >= q1 )

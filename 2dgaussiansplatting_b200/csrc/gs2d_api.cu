@@ -125,6 +125,8 @@ struct gs2d_ctx
 
 	// asynchronous target upload (gs2d_set_target_rgba8_async): H2D on its own stream into one of two device staging
 	// buffers; the u8 -> float conversion is enqueued on the main stream by the next forward (apply_pending_target)
+	// second stream of an iteration: the row table kernel runs beside the scan / place / rank kernels (SideStream)
+	SideStream side{};
 	cudaStream_t copy_stream = nullptr;
 	uint8_t* ustage[2] = { nullptr, nullptr };
 	size_t ustage_bytes = 0;
@@ -359,7 +361,17 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->comm && g_nccl.CommDestroy )
 		g_nccl.CommDestroy( c->comm );
 	Buffers& b = c->b;
+	if( c->side.stream )
+	{
+		cudaStreamSynchronize( c->side.stream );
+		cudaStreamDestroy( c->side.stream );
+	}
+	if( c->side.ev_fork )
+		cudaEventDestroy( c->side.ev_fork );
+	if( c->side.ev_join )
+		cudaEventDestroy( c->side.ev_join );
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
+	                 b.rowrec,     b.rowtab,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots };
@@ -403,7 +415,8 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	if( !out )
 		return GS2D_ERR_INVALID;
 	*out = nullptr;
-	if( W <= 0 || H <= 0 || n_splats < 0 || n_images <= 0 || W > 4096 * GS2D_TILE || H > 65535 * GS2D_TILE ) // tile columns are 12-bit fields in k_preprocess
+	// tile columns are 12-bit fields in k_preprocess; row spans are packed into 16 bits per end (pack_row_span)
+	if( W <= 0 || H <= 0 || n_splats < 0 || n_images <= 0 || W > 65535 || H > 65535 * GS2D_TILE )
 		return GS2D_ERR_INVALID;
 	if( (long long)n_splats * n_images > 0x7FFF0000ll || n_images > 65535 )
 		return GS2D_ERR_INVALID;
@@ -440,6 +453,9 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	} while( 0 )
 	CKC( cudaSetDevice( device ) );
 	CKC( cudaStreamCreateWithFlags( &c->stream, cudaStreamNonBlocking ) );
+	CKC( cudaStreamCreateWithFlags( &c->side.stream, cudaStreamNonBlocking ) );
+	CKC( cudaEventCreateWithFlags( &c->side.ev_fork, cudaEventDisableTiming ) );
+	CKC( cudaEventCreateWithFlags( &c->side.ev_join, cudaEventDisableTiming ) );
 	prepare_forward_pdl();
 	prepare_backward_pdl();
 	cudaGetLastError(); // a refused carveout hint is not an error of this call
@@ -465,10 +481,7 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 		g.n_slices *= 2;
 	g.slice_size = std::max( 1, ( n_splats + g.n_slices - 1 ) / g.n_slices );
 	if( (long long)g.n_tiles_total * g.n_slices > 0x7FFF0000ll )
-	{
-		delete c;
-		return GS2D_ERR_INVALID;
-	}
+		return fail( GS2D_ERR_INVALID );
 	g.min_throughput = c->hp.min_throughput;
 	set_band( c, 0, 1 );
 
@@ -481,6 +494,12 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.adam_m, plane_bytes ) );
 	CKC( cudaMalloc( &b.adam_v, plane_bytes ) );
 	CKC( cudaMalloc( &b.rec, sizeof( SplatRec ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.rowrec, sizeof( RowRec ) * (size_t)std::max( g.n_total, 1 ) ) );
+	// row table: 512 bytes per splat; cleared once - the blend looks every staged entry up, also those whose rows are
+	// not in the table (their words are overwritten by the in-kernel solve, build_words)
+	CKC( cudaMalloc( &b.rowtab, sizeof( unsigned ) * GS2D_ROWTAB_STRIDE * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMemset( b.rowtab, 0, sizeof( unsigned ) * GS2D_ROWTAB_STRIDE * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMemset( b.rowrec, 0xff, sizeof( RowRec ) * (size_t)std::max( g.n_total, 1 ) ) );
 	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
 	// + the 8-byte overflow counter of the slot binning, cleared together with the counters
 	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) ) );
@@ -859,7 +878,7 @@ static int enqueue_forward( gs2d_ctx* c )
 	int rcp = apply_pending_target( c );
 	if( rcp )
 		return rcp;
-	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr, c->slot_binning );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, c->stream, nullptr, c->slot_binning, &c->side );
 	c->launches += launch_forward( c->g, c->b, c->sorted_buf, true, c->stream );
 	c->launches += launch_finalize_loss( c->g, c->b, c->stream );
 	c->have_forward = true;
@@ -972,7 +991,8 @@ static int enqueue_iteration( gs2d_ctx* c )
 	if( pr )                                                                                                          \
 	cudaEventRecord( pr->ev[i], s )
 	PROF( 0 );
-	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr, c->slot_binning );
+	c->launches += launch_preprocess_and_bin( c->g, c->b, &c->sorted_buf, s, pr ? pr->ev[1] : nullptr, c->slot_binning,
+	                                          gs2d_tune( "GS2D_SIDE_STREAM", 1 ) ? &c->side : nullptr );
 	PROF( 2 );
 	if( gs2d_pdl_usable() )
 	{
@@ -1109,6 +1129,14 @@ static int resolve( gs2d_ctx* c )
 			}
 			snprintf( c->err, sizeof( c->err ), "a peer-memory barrier timed out (a rank died or the ranks' call sequences diverged)" );
 			return GS2D_ERR_NCCL;
+		}
+		if( s.nonfinite )
+		{
+			// the device froze at the failing iteration (DevState::frozen): nothing enqueued behind it advanced
+			c->expected_iteration = s.iteration;
+			adapt_binning( c );
+			collect_profile( c );
+			return GS2D_ERR_NONFINITE;
 		}
 		const long long missing = c->expected_iteration - (long long)s.iteration;
 		if( s.need_capacity == 0 && missing <= 0 )

@@ -18,6 +18,11 @@
 // Per entry the warp reduces 8 values (3 colour sums + 5 moments) over its lanes with a transposed butterfly
 // (9 shuffles instead of 40); at the end of a round lane k turns the moments of entry k into the reference's
 // d{pos, sx, sy, rot} with the hoisted per-splat factors and issues ONE red.global.add.f32 per (tile, splat, parameter).
+//
+// Arithmetic modes (template parameter EXACT, tuning knob GS2D_EXACT; gs2d_forward.cu): in both, alpha and the
+// transmittance chain are evaluated exactly as the forward kernel of the same mode evaluates them, so the two passes
+// walk the same live set. Relaxed mode reads the pre-scaled record (SplatRec), needs two FMAs for alpha's argument
+// and gets d/d opacity from the moments (sum g*G = sum g*alpha / opacity) instead of a sum of its own.
 #include "gs2d_blend.cuh"
 
 
@@ -99,7 +104,7 @@ __device__ __forceinline__ void reduce_group( const float ( *stg )[STAGE_STRIDE]
 
 // PDL: launched behind k_forward<.., true> with programmatic stream serialization; waits for its own tile's forward
 // pass instead of the whole grid (gs2d_blend.cuh).
-template <int MINB, bool OPACITY, bool COUNT, bool PDL>
+template <int MINB, bool OPACITY, bool COUNT, bool PDL, bool EXACT>
 __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const SplatRec* __restrict__ rec,
                                                               const unsigned* __restrict__ vals,
                                                               const uint2* __restrict__ tile_range,
@@ -112,7 +117,11 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
                                                               const unsigned* tile_done )
 {
 	if( st->need_capacity )
+	{
+		if( PDL )
+			pdl_grid_wait();
 		return;
+	}
 	__shared__ TileSmem<2> sm;
 	// Cross-lane sums. Every lane parks its 8 partial sums of a visited entry here (two 128-bit stores); after two
 	// entries the warp adds them up transposed (reduce_group: 16 conflict-free loads + adds and one shuffle for two
@@ -142,7 +151,11 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 	const uint2 range = tile_range[tile_id];
 	const unsigned start = range.x, end = range.y;
 	if( start >= end )
+	{
+		if( PDL )
+			pdl_grid_wait(); // an empty tile's forward warp still writes its pixels and loss partial
 		return;
+	}
 	if( PDL )
 	{
 		// tile_range and the lists were complete before k_forward started; the tile's pixels and coverage words are
@@ -151,6 +164,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		{
 			if( lane == 0 )
 				atomicExch( const_cast<int*>( &st->peer_fault ), 2 );
+			pdl_grid_wait();
 			return;
 		}
 	}
@@ -211,7 +225,11 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			cp_async_wait<0>();
 		__syncwarp();
 		uint4 cwa, cwb;
-		unsigned ent = touching_entries( sm, stage, nb, lane, cwa, cwb );
+		touching_entries( sm, stage, nb, lane, cwa, cwb );
+		// entries that cover a pixel that is live now (lane k tests entry k), as in k_forward
+		unsigned ent = __ballot_sync( 0xffffffffu, ( ( cwa.x & live[0] ) | ( cwa.y & live[1] ) | ( cwa.z & live[2] ) |
+		                                             ( cwa.w & live[3] ) | ( cwb.x & live[4] ) | ( cwb.y & live[5] ) |
+		                                             ( cwb.z & live[6] ) | ( cwb.w & live[7] ) ) != 0u );
 
 		unsigned visited = 0;
 		unsigned grp_n = 0u, grp_k = 0u; // visited entries parked in stage4, their list positions (8 bits each)
@@ -231,11 +249,13 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				continue;
 			visited |= 1u << k;
 			const SplatRec& s = sm.rec[stage][k];
-			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py b d
-			const float4 q1 = *reinterpret_cast<const float4*>( &s.a );  // a cr cg cb
+			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py B D
+			const float4 q1 = *reinterpret_cast<const float4*>( &s.A );  // A cr cg cb
 			const float op = s.op;
 			const float vx0 = xsub( fpx0, q0.x ), vx1 = xsub( fpx1, q0.x );
-			const float avx0 = xmul( q1.x, vx0 ), avx1 = xmul( q1.x, vx1 );
+			// per entry and block column: exact  a vx, b vx;  relaxed  s + A vx^2, B vx  (relaxed_alpha)
+			const float avx0 = EXACT ? xmul( q1.x, vx0 ) : __fmaf_rn( __fmul_rn( q1.x, vx0 ), vx0, op );
+			const float avx1 = EXACT ? xmul( q1.x, vx1 ) : __fmaf_rn( __fmul_rn( q1.x, vx1 ), vx1, op );
 			const float bvx0 = xmul( q0.z, vx0 ), bvx1 = xmul( q0.z, vx1 );
 			float gc0 = 0.f, gc1 = 0.f, gc2 = 0.f;          // sum dL/dC * alpha * T            (main.cpp:618-619)
 			float A0[2] = { 0.f, 0.f }, A1[2] = { 0.f, 0.f }; // sum w, sum w*vy per block column   (w = g * alpha)
@@ -251,22 +271,35 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 					nlive += cov ? 1u : 0u;
 				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
 				const float vy = xsub( fpyr[j >> 1], q0.y );
-				// scalar multiplies here: the packed forms of k_forward need aligned register pairs, which at this
-				// kernel's 80-register cap spill (measured: lane bit reloaded from local memory at every visit)
-				const float rx = xadd( avx, xmul( q0.z, vy ) );
-				const float ry = xadd( bvx, xmul( q0.w, vy ) );
-				const float d2 = xadd( xmul( vx, rx ), xmul( vy, ry ) );
-				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
-				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
-				const float G = select_alpha( wl & lanebit, t, t8 ); // main.cpp:610; 0 for uncovered / dead lanes
-				const float alpha = xmul( G, op );           // main.cpp:611 (0 for uncovered / dead lanes)
-				const float wgt = alpha * T[j];              // dC_dc, main.cpp:618
+				float alpha, G = 0.0f, wgt, Tn;
+				if( EXACT )
+				{
+					// scalar multiplies here: the packed forms of k_forward need aligned register pairs, which at this
+					// kernel's 80-register cap spill (measured: lane bit reloaded from local memory at every visit)
+					const float rx = xadd( avx, xmul( q0.z, vy ) );
+					const float ry = xadd( bvx, xmul( q0.w, vy ) );
+					const float d2 = xadd( xmul( vx, rx ), xmul( vy, ry ) );
+					const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
+					const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
+					// alpha exactly as k_forward forms it (main.cpp:610-611): select AFTER the multiply, so that a NaN / inf
+					// opacity cannot leak into uncovered or dead lanes (0 * NaN) and make the two passes' live sets differ
+					alpha = select_alpha( wl & lanebit, t, xmul( t8, op ) );
+					if( OPACITY )
+						G = select_alpha( wl & lanebit, t, t8 );
+					wgt = alpha * T[j];                      // dC_dc, main.cpp:618
+					Tn = xmul( T[j], xsub( 1.0f, alpha ) );  // main.cpp:707
+				}
+				else
+				{
+					alpha = relaxed_alpha( wl & lanebit, vy, q0.w, bvx, avx );
+					wgt = __fmul_rn( T[j], alpha );          // == k_forward's T * alpha
+					Tn = __fsub_rn( T[j], wgt );             // == k_forward's transmittance chain
+				}
 				gc0 = fmaf( dLr[j], wgt, gc0 );
 				gc1 = fmaf( dLg[j], wgt, gc1 );
 				gc2 = fmaf( dLb[j], wgt, gc2 );
 				const float D = T[j] * fmaf( dLb[j], q1.w, fmaf( dLg[j], q1.z, dLr[j] * q1.y ) );
 				const float oma = xsub( 1.0f, alpha );
-				const float Tn = xmul( T[j], oma );          // main.cpp:707
 				const bool dead = Tn < min_T;
 				float Qn = fmaf( -alpha, D, Q[j] );
 				Qn = dead ? 0.0f : Qn;                       // nothing behind a dead pixel: the reference's S is exactly 0
@@ -280,12 +313,14 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				A0[j & 1] += ga;
 				A1[j & 1] += gav;
 				A2 = fmaf( gav, vy, A2 );
-				if( OPACITY )
+				if( OPACITY && EXACT )
 					vop = fmaf( gsum, G, vop );
 				T[j] = Tn;
 				Q[j] = Qn;
 				live[j] = __ballot_sync( 0xffffffffu, !dead );
 			}
+			if( OPACITY && !EXACT )
+				vop = A0[0] + A0[1]; // sum g*alpha = opacity * sum g*G: divided by the opacity in the flush
 			// per-lane moments of w: vx is constant per lane and block column
 			float v[8];
 			v[0] = gc0;
@@ -328,7 +363,18 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			const float4 m0 = *reinterpret_cast<const float4*>( &sm.words[stage][lane][0] ); // dcr dcg dcb Mx
 			const float4 m1 = *reinterpret_cast<const float4*>( &sm.words[stage][lane][4] ); // My Mxx Mxy Myy
 			const SplatRec& s = sm.rec[stage][lane];
-			const float a = s.a, b = s.b, d = s.d;
+			// inv_cov: as stored (exact) or recovered from the pre-scaled record (relaxed: A = -s a/16, B = -s b/8,
+			// D = -s d/16, s = opacity^(1/8) > 0 for every splat that contributed anything)
+			float a = s.A, b = s.B, d = s.D, inv_op = 0.0f;
+			if( !EXACT )
+			{
+				const float is = s.op > 0.0f ? __frcp_rn( s.op ) : 0.0f;
+				a *= -16.0f * is;
+				b *= -8.0f * is;
+				d *= -16.0f * is;
+				const float is2 = is * is, is4 = is2 * is2;
+				inv_op = is4 * is4; // 1 / opacity
+			}
 			const float c = s.cosT, sn = s.sinT;
 			const float c2 = c * c, s2 = sn * sn, sc = sn * c;
 			const float Mx = m0.w, My = m1.x, Mxx = m1.y, Mxy = m1.z, Myy = m1.w;
@@ -346,7 +392,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			atomicAdd( gp + PL_SY * np, s.isy3 * ( fmaf( s2, Mxx, fmaf( c2, Myy, -tsc ) ) ) );
 			atomicAdd( gp + PL_ROT * np, s.rotc * ( fmaf( c2 - s2, Mxy, -sc * ( Mxx - Myy ) ) ) );
 			if( OPACITY )
-				atomicAdd( gp + PL_OP * np, vop_tot[lane] );
+				atomicAdd( gp + PL_OP * np, EXACT ? vop_tot[lane] : vop_tot[lane] * inv_op );
 		}
 
 		unsigned anylive = 0;
@@ -366,13 +412,15 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		if( lane == 0 )
 			atomicAdd( &live_slots[tile_id & ( GS2D_LIVE_SLOTS - 1 )], (unsigned long long)nlive );
 	}
+	if( PDL )
+		pdl_grid_wait();
 }
 
-template <bool OPACITY>
-static void launch_backward_pdl( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf,
-                                 unsigned long long* slots, cudaStream_t s )
+template <int MINB, bool OPACITY, bool COUNT, bool PDL, bool EXACT>
+static void launch_backward_as( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf,
+                                unsigned long long* slots, cudaStream_t s )
 {
-	auto kernel = k_backward<GS2D_BWD_MINB_DEFAULT, OPACITY, false, true>;
+	auto kernel = k_backward<MINB, OPACITY, COUNT, PDL, EXACT>;
 	cudaLaunchAttribute attr[1];
 	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 	attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -382,19 +430,42 @@ static void launch_backward_pdl( dim3 grid, const Geometry& g, const Buffers& b,
 	cfg.dynamicSmemBytes = 0;
 	cfg.stream = s;
 	cfg.attrs = attr;
-	cfg.numAttrs = 1;
+	cfg.numAttrs = PDL ? 1 : 0;
 	cudaLaunchKernelEx( &cfg, kernel, g, (const SplatRec*)b.rec, (const unsigned*)b.vals[sorted_buf],
 	                    (const uint2*)b.tile_range, (const float4*)b.target, (const float4*)b.image,
 	                    (const unsigned*)b.cover, b.grads, slots, (const DevState*)b.state,
-	                    (const unsigned*)b.tile_done );
+	                    (const unsigned*)( PDL ? b.tile_done : nullptr ) );
+}
+template <int MINB, bool PDL, bool COUNT>
+static void launch_backward_minb( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity,
+                                  bool exact, unsigned long long* slots, cudaStream_t s )
+{
+	if( with_opacity )
+	{
+		if( exact )
+			launch_backward_as<MINB, true, COUNT, PDL, true>( grid, g, b, sorted_buf, slots, s );
+		else
+			launch_backward_as<MINB, true, COUNT, PDL, false>( grid, g, b, sorted_buf, slots, s );
+	}
+	else
+	{
+		if( exact )
+			launch_backward_as<MINB, false, COUNT, PDL, true>( grid, g, b, sorted_buf, slots, s );
+		else
+			launch_backward_as<MINB, false, COUNT, PDL, false>( grid, g, b, sorted_buf, slots, s );
+	}
 }
 
 void prepare_backward_pdl()
 {
-	cudaFuncSetAttribute( k_backward<GS2D_BWD_MINB_DEFAULT, false, false, true>,
-	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
-	cudaFuncSetAttribute( k_backward<GS2D_BWD_MINB_DEFAULT, true, false, true>,
-	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
+#define CARVE( OP, EXACT )                                                                                            \
+	cudaFuncSetAttribute( k_backward<GS2D_BWD_MINB_DEFAULT, OP, false, true, EXACT>,                                 \
+	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared )
+	CARVE( false, false );
+	CARVE( true, false );
+	CARVE( false, true );
+	CARVE( true, true );
+#undef CARVE
 }
 
 // PDL twins exist for the default register caps
@@ -416,36 +487,26 @@ int launch_backward( const Geometry& g, const Buffers& b, int sorted_buf, bool w
 	unsigned long long* slots = b.live_slots + 2 * GS2D_LIVE_SLOTS;
 	if( count_live )
 		cudaMemsetAsync( slots, 0, sizeof( unsigned long long ) * GS2D_LIVE_SLOTS, s );
-	if( pdl )
+	const bool exact = gs2d_exact_mode();
+	if( pdl ) // the counting variant is only launched stand-alone (gs2d_backward)
 	{
-		if( with_opacity )
-			launch_backward_pdl<true>( grid, g, b, sorted_buf, slots, s );
-		else
-			launch_backward_pdl<false>( grid, g, b, sorted_buf, slots, s );
+		launch_backward_minb<GS2D_BWD_MINB_DEFAULT, true, false>( grid, g, b, sorted_buf, with_opacity, exact, slots, s );
 		return 1;
 	}
-#define LAUNCH_BWD3( MINB, OP, CNT )                                                                                  \
-	k_backward<MINB, OP, CNT, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,       \
-	                                                      b.image, b.cover, b.grads, slots, b.state, nullptr )
-#define LAUNCH_BWD( MINB )                                                                                            \
-	do                                                                                                                \
-	{                                                                                                                 \
-		if( with_opacity && count_live )                                                                              \
-			LAUNCH_BWD3( MINB, true, true );                                                                          \
-		else if( with_opacity )                                                                                       \
-			LAUNCH_BWD3( MINB, true, false );                                                                         \
-		else if( count_live )                                                                                         \
-			LAUNCH_BWD3( MINB, false, true );                                                                         \
-		else                                                                                                          \
-			LAUNCH_BWD3( MINB, false, false );                                                                        \
-	} while( 0 )
-	switch( gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT ) )
+	const int minb = gs2d_tune( "GS2D_BWD_MINB", GS2D_BWD_MINB_DEFAULT );
+	if( count_live )
 	{
-	case 16: LAUNCH_BWD( 16 ); break;
-	case 20: LAUNCH_BWD( 20 ); break;
-	default: LAUNCH_BWD( 24 ); break;
+		if( minb == 20 )
+			launch_backward_minb<20, false, true>( grid, g, b, sorted_buf, with_opacity, exact, slots, s );
+		else
+			launch_backward_minb<24, false, true>( grid, g, b, sorted_buf, with_opacity, exact, slots, s );
 	}
-#undef LAUNCH_BWD
-#undef LAUNCH_BWD3
+	else
+	{
+		if( minb == 20 )
+			launch_backward_minb<20, false, false>( grid, g, b, sorted_buf, with_opacity, exact, slots, s );
+		else
+			launch_backward_minb<24, false, false>( grid, g, b, sorted_buf, with_opacity, exact, slots, s );
+	}
 	return 1;
 }

@@ -85,11 +85,14 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 	}
 }
 
+// relaxed: write the record in the scaled form the relaxed-arithmetic blend kernels read (SplatRec, gs2d_internal.cuh)
+// rowtab: 1 = splats of at most GS2D_ROWTAB_TILE_ROWS tile rows get their rows solved by k_row_table (else every
+// splat is left to the blend kernels' in-kernel solve: GS2D_ROWTAB=0, the A/B reference)
 template <bool SLOTS>
 __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const float* __restrict__ params,
-                                                               SplatRec* __restrict__ rec, PairOut out,
-                                                               unsigned long long capacity, int cull,
-                                                               DevState* __restrict__ st )
+                                                               SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
+                                                               PairOut out, unsigned long long capacity, int cull,
+                                                               int relaxed, int rowtab, DevState* __restrict__ st )
 {
 	const int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -117,7 +120,9 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		// 2 px and 1e-3 relative cover the truncation and the float error of the exact bound. NaNs fall through.
 		const float hmax = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f;
 		const bool off_band = py + hmax < (float)( g.band_ty0 * GS2D_TILE ) || py - hmax > (float)( g.band_ty1 * GS2D_TILE );
-		if( !off_band )
+		if( off_band )
+			rowrec[gi].tyr = ROWREC_NONE; // k_row_table looks at every splat
+		else
 		{
 			// cosf/sinf of the reference are glibc's (< 1 ulp, almost always correctly rounded). Evaluate in double and
 			// round once: agrees with it bit for bit except in rare double-rounding cases.
@@ -130,30 +135,67 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			const float det = ge.det, a = ge.a, b = ge.b, d = ge.d;
 			const int begY = ge.begY, endY = ge.endY;
 
+			const float op = params[PL_OP * g.n_pad + gi];
 			SplatRec r;
 			r.px = px;
 			r.py = py;
-			r.a = a;
-			r.b = b;
-			r.d = d;
+			if( relaxed )
+			{
+				// s = opacity^(1/8) (three correctly rounded square roots), at most 1: alpha = ( s * (1 - d2/16) )^8 with
+				// the product clamped to [0, 1] by the blend's saturating FMA. The scalings by 1/8, 1/16 are exact.
+				const float sop = fminf( xsqrt( xsqrt( xsqrt( op ) ) ), 1.0f );
+				r.A = xmul( sop, xmul( a, -0.0625f ) );
+				r.B = xmul( sop, xmul( b, -0.125f ) );
+				r.D = xmul( sop, xmul( d, -0.0625f ) );
+				r.op = sop;
+			}
+			else
+			{
+				r.A = a;
+				r.B = b;
+				r.D = d;
+				r.op = op;
+			}
 			r.cr = params[PL_CR * g.n_pad + gi];
 			r.cg = params[PL_CG * g.n_pad + gi];
 			r.cb = params[PL_CB * g.n_pad + gi];
-			r.op = params[PL_OP * g.n_pad + gi];
-			r.begY = begY;
-			r.endY = endY;
+			r.idx = (unsigned)gi;
 			// hoisted backward invariants, main.cpp:658, :661, :682 (same operand order)
 			r.rotc = xdiv( xsub( xmul( sx, sx ), xmul( sy, sy ) ), xmul( xmul( xmul( sx, sx ), sy ), sy ) );
 			r.cosT = c;
 			r.sinT = s;
 			r.isx3 = xdiv( 1.0f, xmul( xmul( sx, sx ), sx ) );
 			r.isy3 = xdiv( 1.0f, xmul( xmul( sy, sy ), sy ) );
+			// rows of the splat inside the image and inside this rank's band, in tile rows; the row table holds splats
+			// of at most GS2D_ROWTAB_TILE_ROWS tile rows (whole image: the flag must not depend on the band)
+			const int ry0 = max( begY, 0 ), ry1 = min( endY, g.H - 1 );
+			const bool in_table = rowtab && ry0 <= ry1 && ( ry1 / GS2D_TILE - ry0 / GS2D_TILE ) < GS2D_ROWTAB_TILE_ROWS;
+			r.flags = in_table ? SPLAT_IN_TABLE : 0u;
 			float4* dst = reinterpret_cast<float4*>( rec + gi );
 			const float4* src = reinterpret_cast<const float4*>( &r );
 			dst[0] = src[0];
 			dst[1] = src[1];
 			dst[2] = src[2];
 			dst[3] = src[3];
+			RowRec rr;
+			rr.px = px;
+			rr.py = py;
+			rr.a = a;
+			rr.b = b;
+			rr.d = d;
+			rr.begY = begY;
+			rr.endY = endY;
+			rr.tyr = ROWREC_NONE;
+			if( in_table )
+			{
+				const int t0 = max( ry0 / GS2D_TILE, g.band_ty0 ), t1 = min( ry1 / GS2D_TILE, g.band_ty1 - 1 );
+				if( t0 <= t1 )
+					rr.tyr = (unsigned)t0 | ( (unsigned)t1 << 16 );
+			}
+			float4* rdst = reinterpret_cast<float4*>( rowrec + gi );
+			const float4* rsrc = reinterpret_cast<const float4*>( &rr );
+			rdst[0] = rsrc[0];
+			rdst[1] = rsrc[1];
 
 			// Conservative tile rectangle. Rows: exactly the reference's [begY, endY]. Columns: every chord of the 3-sigma
 			// ellipse lies within pos.x +- 3*sqrt(cov[0][0]) = 3*sqrt(d*det); widened by 2 px + 1e-4 relative for the
@@ -281,6 +323,39 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		}
 		__syncwarp();
 	}
+}
+
+// ---------------------------------------------------------------------------------------------- row table ---
+// The exact scan-line footprint (solve_quadratic per image row, main.cpp:171-185, :492-509: two IEEE divisions and a
+// square root) used to be solved by the forward blend for every (staged list entry, tile row): 16 rows of every
+// entry of every tile a splat touches, ~4 tiles per tile row, by warps that spend a quarter of their issue slots on
+// it. Here every (splat, image row) is solved ONCE, by a dense grid: one thread per slot of the splat's ring of
+// GS2D_ROWTAB_TILE_ROWS 16-row blocks (a warp = two blocks = 128 contiguous bytes). Slots of tile rows the splat does
+// not reach inside this rank's band are not written (nothing reads them); rows of a reached tile row that lie outside
+// [begY, endY] are written as empty, so the blend needs no row test of its own. Same arithmetic as the in-kernel
+// solve (row_span), so the coverage words - and the image - are bit-identical to it.
+__global__ void __launch_bounds__( 256 ) k_row_table( Geometry g, const RowRec* __restrict__ rowrec,
+                                                      unsigned* __restrict__ rowtab )
+{
+	const unsigned t = blockIdx.x * 256u + threadIdx.x;
+	const unsigned gi = t / GS2D_ROWTAB_STRIDE, slot = t % GS2D_ROWTAB_STRIDE;
+	if( gi >= (unsigned)g.n_total )
+		return;
+	const RowRec* rr = rowrec + gi;
+	const unsigned tyr = rr->tyr;
+	if( tyr == ROWREC_NONE )
+		return;
+	const int t0 = (int)( tyr & 0xffffu ), t1 = (int)( tyr >> 16 );
+	// the tile row of [t0, t0 + 8) that lives at this ring position
+	const int ty = t0 + ( ( (int)( slot / GS2D_TILE ) - t0 ) & ( GS2D_ROWTAB_TILE_ROWS - 1 ) );
+	if( ty > t1 )
+		return;
+	const float4 q0 = *reinterpret_cast<const float4*>( rr );       // px py a b
+	const float4 q1 = *reinterpret_cast<const float4*>( &rr->d );   // d begY endY tyr
+	const int y = ty * GS2D_TILE + (int)( slot % GS2D_TILE );
+	int begX = 0, endX = 0;
+	const bool any = row_span( q0.x, q0.y, q0.z, q0.w, q1.x, __float_as_int( q1.y ), __float_as_int( q1.z ), y, g.H, begX, endX );
+	rowtab[(size_t)gi * GS2D_ROWTAB_STRIDE + slot] = pack_row_span( any, begX, endX, g.W );
 }
 
 // ------------------------------------------------------------------------------- exclusive scan of the counts ---
@@ -524,8 +599,10 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 }
 
 // ---------------------------------------------------------------------------------------------------- launch ---
+bool gs2d_exact_mode() { return gs2d_tune( "GS2D_EXACT", 0 ) != 0; }
+
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
-                               cudaEvent_t after_emit, bool use_slots )
+                               cudaEvent_t after_emit, bool use_slots, const SideStream* side )
 {
 	int launches = 0;
 	*sorted_buf = 0; // the ordered lists end up in vals[0]
@@ -547,13 +624,39 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	// the overflow counter sits behind the bucket counters and is cleared with them
 	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + (size_t)g.nt_pad * g.n_slices );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
+	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
 	if( slots )
-		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
+		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		                                               relaxed, rowtab, b.state );
 	else
-		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ), b.state );
+		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		                                                relaxed, rowtab, b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
+	// The row table needs the RowRecs only, the scan / place / rank kernels the bucket counters only: the two run side
+	// by side (k_row_table is issue-bound, the binning kernels wait on L2 / HBM most of the time).
+	bool forked = false;
+	if( rowtab )
+	{
+		const unsigned rt_blocks = (unsigned)( ( (size_t)g.n_total * GS2D_ROWTAB_STRIDE + 255 ) / 256 );
+		cudaStream_t rs = s;
+		if( side && side->stream )
+		{
+			cudaEventRecord( side->ev_fork, s );
+			cudaStreamWaitEvent( side->stream, side->ev_fork, 0 );
+			rs = side->stream;
+			forked = true;
+		}
+		k_row_table<<<rt_blocks, 256, 0, rs>>>( g, b.rowrec, b.rowtab );
+		launches += 1;
+		if( forked )
+			cudaEventRecord( side->ev_join, rs );
+	}
+	auto join = [&]() {
+		if( forked )
+			cudaStreamWaitEvent( s, side->ev_join, 0 );
+	};
 	// only the buckets of this rank's band of tile rows hold entries (one contiguous window for a single image)
 	unsigned lo = 0, hi = nbk;
 	if( g.n_images == 1 )
@@ -562,7 +665,10 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		hi = (unsigned)g.band_ty1 * (unsigned)g.tiles_x * (unsigned)g.n_slices;
 	}
 	if( hi <= lo )
+	{
+		join();
 		return launches;
+	}
 	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
 	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, lo, hi, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
@@ -581,5 +687,6 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		                                                      b.vals[0], b.tile_range, lo, hi, b.state, nullptr );
 	}
 	launches += 4;
+	join();
 	return launches;
 }

@@ -28,6 +28,56 @@ __device__ __forceinline__ float select_alpha( unsigned covered, float t, float 
 	return r;
 }
 
+// ---- relaxed arithmetic (GS2D_EXACT=0, the default) ------------------------------------------------------------------
+// Everything below is written with explicit _rn intrinsics, not operators: the forward and the backward kernel must
+// evaluate the SAME alpha and transmittance chain bit for bit (the backward re-walks the forward's live set), which
+// must not depend on what the compiler chooses to contract in either of them.
+// fma with the result clamped to [0, 1] (FFMA.SAT; NaN -> 0): s * (1 - d2/16) is at most s <= 1, and everything
+// below exp_approx's cut-off (main.cpp:60) that matters is negative.
+__device__ __forceinline__ float fma_sat( float a, float b, float c )
+{
+	float r;
+	asm( "fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"( r ) : "f"( a ), "f"( b ), "f"( c ) );
+	return r;
+}
+// covered != 0 ? value : 0 (LOP3 with predicate output + FSEL)
+__device__ __forceinline__ float select_covered( unsigned covered, float value )
+{
+	float r;
+	asm( "{\n\t.reg .pred pc;\n\t"
+	     "setp.ne.u32 pc, %1, 0;\n\t"
+	     "selp.f32 %0, %2, 0f00000000, pc;\n\t}"
+	     : "=f"( r )
+	     : "r"( covered ), "f"( value ) );
+	return r;
+}
+// alpha of one pixel in relaxed arithmetic: t = clamp( axx + vy * ( bvx + D * vy ), 0, 1 ) with the per-entry column
+// terms bvx = B vx, axx = s + A vx^2 (SplatRec: A, B, D pre-scaled by -s/16, -s/8, -s/16, s = opacity^(1/8));
+// alpha = t^8 = opacity * (1 - d2/16)^8 = main.cpp:527 up to rounding. 0 for uncovered or dead lanes.
+__device__ __forceinline__ float relaxed_alpha( unsigned covered, float vy, float D, float bvx, float axx )
+{
+	const float t = fma_sat( vy, __fmaf_rn( D, vy, bvx ), axx );
+	const float t2 = __fmul_rn( t, t ), t4 = __fmul_rn( t2, t2 );
+	return select_covered( covered, __fmul_rn( t4, t4 ) );
+}
+
+// statistics of the counting variants: 1 if this lane's pixel is covered and live (GS2D_VISIT_HIST: also the
+// developer histograms of useful lanes per block visit and of live pixels left in the tile)
+__device__ __forceinline__ unsigned count_visit( unsigned wl, unsigned lanebit, const unsigned live[8], int visit_hist,
+                                                 int lane, unsigned long long ( *hist )[33] )
+{
+	if( visit_hist && lane == 0 )
+	{
+		atomicAdd( &hist[0][__popc( wl )], 1ull );
+		unsigned tl = 0;
+#pragma unroll
+		for( int jj = 0; jj < 8; jj++ )
+			tl += __popc( live[jj] );
+		atomicAdd( &hist[1][min( 32u, ( tl + 7u ) / 8u )], 1ull );
+	}
+	return ( wl & lanebit ) != 0u ? 1u : 0u;
+}
+
 // Two floats in an aligned register pair, and the packed multiply mul.rn.f32x2 (SASS FMUL2): each half is the IEEE
 // product, exactly __fmul_rn, but the pair costs ONE issue slot (the blend kernels are issue-bound).
 // Only multiplies are packed: ptxas contracts a packed multiply feeding a packed add into FFMA2 (one rounding, not
@@ -58,13 +108,21 @@ __device__ __forceinline__ f32x2 xmul2( f32x2 a, f32x2 b )
 //   * every forward warp issues griddepcontrol.launch_dependents first thing: the backward grid becomes eligible
 //     once the LAST forward warp has started, i.e. all forward warps already hold their SM slots (no deadlock:
 //     a waiting backward warp can never keep a forward warp from being scheduled);
-//   * the backward grid is launched with the programmatic-stream-serialization attribute and never executes
+//   * the backward grid is launched with the programmatic-stream-serialization attribute and does not START with
 //     griddepcontrol.wait (that would wait for the whole forward grid); instead the warp of tile t spins on
-//     tile_done[t], which the forward warp of t stores with release semantics after its last global write.
+//     tile_done[t], which the forward warp of t stores with release semantics after its last global write. Every
+//     backward warp ENDS with griddepcontrol.wait (pdl_grid_wait) to keep the stream's transitive ordering.
 // Backward warps are dispatched in tile order, so the tiles they ask for finished long ago; the wait is a single
 // acquire load except for the last wave. What the backward reads of the forward's output goes through L2
 // (cp.async.cg, ld.global.cg): L1 is not coherent with stores of a concurrently running grid.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile( "griddepcontrol.launch_dependents;" ::: "memory" ); }
+// Executed by every backward warp as its LAST instruction (also on the early-exit paths: empty tile, capacity
+// overflow): the backward grid then completes only after the whole forward grid has completed and flushed, so
+// whatever follows the backward grid on the stream (k_finalize_loss reads loss_partial / live_slots of ALL forward
+// warps, empty tiles included) is transitively ordered behind the forward grid, as PTX requires of a dependent of a
+// grid that uses launch_dependents. Free in practice: the forward grid is in its tail when the first backward warp
+// starts, and a backward tile runs longer than that tail.
+__device__ __forceinline__ void pdl_grid_wait() { asm volatile( "griddepcontrol.wait;" ::: "memory" ); }
 __device__ __forceinline__ void pdl_publish_tile( unsigned* flag, int lane )
 {
 	__threadfence(); // this lane's pixel / coverage / loss stores are performed at gpu scope
@@ -114,25 +172,68 @@ __device__ __forceinline__ void gather_record( TileSmem<WSTAGES>& sm, int stage,
 		for( int q = 0; q < QUADS; q++ )
 			cp_async16( dst + q, src + q );
 	}
+	else
+		sm.rec[stage][lane].idx = 0u; // a slot beyond the batch: build_words looks it up like any other (splat 0 exists)
 }
 
-// Exact footprint of the nb staged entries of `stage`: 16 rows x nb entries = up to 512 solves, 16 per lane.
-// Lane (h = lane >> 4, r = lane & 15) solves row r of entries 2i + h and scatters the 16-bit row mask as two bytes
-// into the block words of the entry.
-__device__ __forceinline__ void solve_batch( TileSmem<1>& sm, int stage, int nb, int lane, int tile_x0, int tile_y0,
+// Exact coverage words of the nb staged entries of `stage`: 16 rows x nb entries. Lane (h = lane >> 4, r = lane & 15)
+// handles row r of entries 2i + h: it fetches the packed span of (splat, image row) from the row table (k_row_table
+// solved it once for all the tiles the row crosses; the 16 rows of an entry are 64 contiguous bytes), clips it to
+// the tile's 16 columns and scatters the mask as two bytes into the block words of the entry. Four entries per lane
+// are in flight at a time.
+// Splats that are not in the row table (taller than GS2D_ROWTAB_TILE_ROWS tile rows, or GS2D_ROWTAB=0) are solved
+// here, in a second loop that a warp enters only if its batch holds one: the reference's quadratic per (entry, tile
+// row) from the unscaled RowRec (row_mask, gs2d_footprint.cuh) - same arithmetic as k_row_table, same words.
+__device__ __forceinline__ void build_words( TileSmem<1>& sm, int stage, int nb, int lane, int tile_x0, int tile_y,
+                                             const unsigned* __restrict__ rowtab, const RowRec* __restrict__ rowrec,
                                              int W, int H )
 {
 	const int h = lane >> 4, r = lane & 15;
-	const int y = tile_y0 + r;
+	const unsigned ring = (unsigned)( ( tile_y & ( GS2D_ROWTAB_TILE_ROWS - 1 ) ) * GS2D_TILE + r );
 	// byte (r & 3) of word 2*(r >> 2) of entry h; the right half of the row is 4 bytes on, the next entry pair 64
-	unsigned char* wb = reinterpret_cast<unsigned char*>( &sm.words[0][h][0] ) + ( r >> 2 ) * 8 + ( r & 3 );
-	const SplatRec* s = &sm.rec[stage][h];
-#pragma unroll 2
-	for( int k = h; k < nb; k += 2, s += 2, wb += 64 )
+	unsigned char* wb0 = reinterpret_cast<unsigned char*>( &sm.words[0][h][0] ) + ( r >> 2 ) * 8 + ( r & 3 );
 	{
-		const unsigned m = row_mask( s->px, s->py, s->a, s->b, s->d, s->begY, s->endY, y, tile_x0, W, H );
-		wb[0] = (unsigned char)( m & 0xffu );
-		wb[4] = (unsigned char)( m >> 8 );
+		// every staged slot is processed, valid or not (gather_record gives the slots beyond the batch index 0), and
+		// every entry is looked up, in the table or not (the table is allocated for every splat and was cleared once):
+		// no predicate in the loop; entries that are not in the table are overwritten by the second loop
+		unsigned char* wb = wb0;
+		const SplatRec* s = &sm.rec[stage][h];
+		const unsigned* tab = rowtab + ring;
+#pragma unroll 1
+		for( int k0 = h; k0 < nb; k0 += 8, s += 8, wb += 256 )
+		{
+			unsigned span[4];
+#pragma unroll
+			for( int u = 0; u < 4; u++ )
+				span[u] = __ldg( tab + (size_t)s[2 * u].idx * GS2D_ROWTAB_STRIDE );
+#pragma unroll
+			for( int u = 0; u < 4; u++ )
+			{
+				const unsigned m = mask_of_span( span[u], tile_x0 );
+				wb[64 * u] = (unsigned char)m;
+				wb[64 * u + 4] = (unsigned char)( m >> 8 );
+			}
+		}
+	}
+	const bool mine_big = lane < nb && ( sm.rec[stage][lane].flags & SPLAT_IN_TABLE ) == 0u;
+	if( __any_sync( 0xffffffffu, mine_big ) )
+	{
+		const int y = tile_y * GS2D_TILE + r;
+		unsigned char* wb = wb0;
+		const SplatRec* s = &sm.rec[stage][h];
+#pragma unroll 1
+		for( int k = h; k < nb; k += 2, s += 2, wb += 64 )
+		{
+			if( s->flags & SPLAT_IN_TABLE )
+				continue;
+			const RowRec* rr = rowrec + s->idx;
+			const float4 q0 = __ldg( reinterpret_cast<const float4*>( rr ) );     // px py a b
+			const float4 q1 = __ldg( reinterpret_cast<const float4*>( rr ) + 1 ); // d begY endY tyr
+			const unsigned m = row_mask( q0.x, q0.y, q0.z, q0.w, q1.x, __float_as_int( q1.y ), __float_as_int( q1.z ), y,
+			                             tile_x0, W, H );
+			wb[0] = (unsigned char)( m & 0xffu );
+			wb[4] = (unsigned char)( m >> 8 );
+		}
 	}
 }
 

@@ -134,14 +134,24 @@ int main( int argc, char** argv )
 		rc = gs2d_step( ctx, chunk, mse.data() );
 		if( rc != GS2D_OK && rc != GS2D_ERR_NONFINITE )
 			CHECK( rc );
-		for( int k = 0; k < chunk; k++, iterations++ )
+		int valid = chunk;
+		if( rc == GS2D_ERR_NONFINITE )
+		{
+			// The device froze in the iteration whose Adam step produced the non-finite parameter; its counter reads that
+			// iteration's index + 1. The reference abort()s there BEFORE printing that iteration's line (main.cpp:752-785
+			// precedes :796-807), so only the lines of the iterations before it are printed.
+			int it_dev = iterations;
+			gs2d_download_state( ctx, 0, nullptr, nullptr, nullptr, nullptr, &it_dev );
+			valid = std::max( 0, std::min( chunk, it_dev - 1 - iterations ) );
+		}
+		for( int k = 0; k < valid; k++, iterations++ )
 			if( iterations % print_every == 0 )
 				printf( "%d itr, mse %.4f\n", iterations, mse[(size_t)k] ); // main.cpp:807
 		fflush( stdout );
 		done += chunk;
 		if( rc == GS2D_ERR_NONFINITE )
 		{
-			fprintf( stderr, "gs2d_fit: non-finite splat parameter - the reference aborts here (main.cpp:752-785)\n" );
+			fprintf( stderr, "gs2d_fit: non-finite splat parameter in iteration %d - the reference aborts here (main.cpp:752-785)\n", iterations );
 			if( save )
 				gs2d_save_checkpoint( ctx, save );
 			gs2d_destroy( ctx );

@@ -1,17 +1,26 @@
 // gs2d_forward.cu — per-tile front-to-back alpha blend (the reference's forward splat loop, main.cpp:419-538,
 // turned inside out: one warp per 16x16 tile, the tile's splat list walked in index order == the reference's order).
 //
-// Per round, GS2D_BATCH list entries are gathered into shared memory with cp.async (double-buffered), the exact
-// scan-line footprint of every (splat, tile row) is solved ONCE (row_mask: main.cpp:489-509 incl. the float quadratic
-// and the x86 truncation) and stored as coverage words of the eight 8x4 pixel blocks of the tile (gs2d_blend.cuh).
-// The warp then walks the entries that touch the tile: a block is visited only when (coverage & live) != 0, and the
-// visit is branch-free: uncovered or dead lanes blend with alpha = 0, which leaves their colour and throughput
-// bit-for-bit unchanged (x + (+0) == x, T * 1 == T).
+// Per round, GS2D_BATCH list entries are gathered into shared memory with cp.async (double-buffered) and the exact
+// scan-line footprint of every (splat, tile row) - solved once per (splat, image row) by k_row_table with the
+// reference's float quadratic and x86 truncation (main.cpp:489-509) - is clipped to the tile and stored as coverage
+// words of the eight 8x4 pixel blocks of the tile (gs2d_blend.cuh).
+// The warp then walks the entries that touch a live pixel of the tile: a block is visited only when
+// (coverage & live) != 0, and the visit is branch-free: uncovered or dead lanes blend with alpha = 0, which leaves
+// their colour and throughput bit-for-bit unchanged (x + (+0) == x, T * 1 == T).
 // A pixel is live while T >= MIN_THROUGHPUT (main.cpp:520); T only decreases, so a dead pixel never revives and a
 // tile stops as soon as all its pixels are dead.
 //
-// Arithmetic: the transmittance/colour chain is evaluated with the reference's operand order and WITHOUT FMA
-// contraction, so the image is bit-identical to the CPU reference whenever cosf/sinf agree (see k_preprocess).
+// Arithmetic, two modes (template parameter EXACT, tuning knob GS2D_EXACT):
+//   exact   : the transmittance/colour chain is evaluated with the reference's operand order and WITHOUT FMA
+//             contraction, so the image is bit-identical to the CPU reference whenever cosf/sinf agree (k_preprocess);
+//             28 issue slots per block visit;
+//   relaxed : (default) what the north star allows - "within a stated FP32 tolerance, blend order preserved":
+//             d2 and exp_approx's 1 + x/8 collapse into two FMAs on per-entry column terms (the record carries the
+//             inverse covariance pre-scaled by -opacity^(1/8)/16), the cut-off t < 1.8e-5 -> 0 (main.cpp:60) becomes
+//             the saturation of that FMA (t in (0, 1.8e-5) gives alpha < 1e-38 instead of 0), colour accumulates as
+//             C += (T alpha) c with FMAs and T -= T alpha: 17 issue slots per block visit. The covered-pixel set
+//             (footprint), the blend order and the T < 1/256 skip rule are the reference's in both modes.
 #include "gs2d_blend.cuh"
 
 // MINB = resident warps (tiles) per SM the register allocation is capped for: 32 -> 64 registers, 24 -> 80, 20 -> 96.
@@ -23,7 +32,7 @@ __device__ unsigned long long g_visit_hist[2][33];
 // PDL (default, GS2D_PDL=0 turns it off; gs2d_blend.cuh): the backward grid is launched with programmatic stream serialization and fills the
 // SM slots the forward pass's last wave frees; a tile's forward warp publishes tile_done[tile] when its image pixels,
 // coverage words and loss partial are written, and the tile's backward warp waits for exactly that.
-template <int MINB, bool COUNT, bool PDL>
+template <int MINB, bool COUNT, bool PDL, bool EXACT>
 __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const SplatRec* __restrict__ rec,
                                                              const unsigned* __restrict__ vals,
                                                              const uint2* __restrict__ tile_range,
@@ -34,7 +43,9 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
                                                              unsigned long long* __restrict__ live_slots,
                                                              unsigned long long* __restrict__ staged_slots,
                                                              const DevState* __restrict__ st, int visit_hist,
-                                                             unsigned* __restrict__ tile_done )
+                                                             unsigned* __restrict__ tile_done,
+                                                             const unsigned* __restrict__ rowtab,
+                                                             const RowRec* __restrict__ rowrec )
 {
 	if( PDL )
 		pdl_launch_dependents(); // the dependent grid may start once every forward warp has got this far (or exited)
@@ -100,18 +111,24 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 		else
 			cp_async_wait<0>();
 		__syncwarp();
-		solve_batch( sm, stage, nb, lane, tile_x0, tile_y0, g.W, g.H );
+		build_words( sm, stage, nb, lane, tile_x0, tile_y, rowtab, rowrec, g.W, g.H );
 		__syncwarp();
 		nstaged += nb;
 		// the coverage words go to HBM for the backward pass (32 bytes per staged entry, coalesced)
 		uint4 cwa, cwb;
-		unsigned ent = touching_entries( sm, 0, nb, lane, cwa, cwb );
+		touching_entries( sm, 0, nb, lane, cwa, cwb );
 		if( lane < nb )
 		{
 			uint4* dst = reinterpret_cast<uint4*>( cover + ( (size_t)base + lane ) * 8 );
 			__stcg( dst, cwa );
 			__stcg( dst + 1, cwb );
 		}
+		// entries worth walking: those that cover a pixel that is still live now (lane k tests entry k). Pixels only
+		// die, so an entry dropped here could not have contributed; one that loses its last live pixel while the
+		// batch is walked fails its eight block tests below.
+		unsigned ent = __ballot_sync( 0xffffffffu, ( ( cwa.x & live[0] ) | ( cwa.y & live[1] ) | ( cwa.z & live[2] ) |
+		                                             ( cwa.w & live[3] ) | ( cwb.x & live[4] ) | ( cwb.y & live[5] ) |
+		                                             ( cwb.z & live[6] ) | ( cwb.w & live[7] ) ) != 0u );
 
 #pragma unroll 1
 		while( ent )
@@ -121,61 +138,71 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[0][k][0] );
 			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[0][k][4] );
 			const unsigned wd[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
-			unsigned hit = 0;
-#pragma unroll
-			for( int j = 0; j < 8; j++ )
-				hit |= wd[j] & live[j];
-			if( hit == 0u )
-				continue;
 			const SplatRec& s = sm.rec[stage][k];
-			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py b d
-			const float4 q1 = *reinterpret_cast<const float4*>( &s.a );  // a cr cg cb
+			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py B D
+			const float4 q1 = *reinterpret_cast<const float4*>( &s.A );  // A cr cg cb
 			const float op = s.op;
 			const float vx0 = xsub( fpx0, q0.x ), vx1 = xsub( fpx1, q0.x );
-			const float avx0 = xmul( q1.x, vx0 ), avx1 = xmul( q1.x, vx1 );
-			const float bvx0 = xmul( q0.z, vx0 ), bvx1 = xmul( q0.z, vx1 );
-			const f32x2 bd = pack2( q0.z, q0.w ), cgb = pack2( q1.z, q1.w ); // packed multiplies: see xmul2
-#pragma unroll
-			for( int j = 0; j < 8; j++ )
+			if( EXACT )
 			{
-				const unsigned wl = wd[j] & live[j];
-				if( wl == 0u ) // warp-uniform: no covered live pixel in this 8x4 block
-					continue;
-				const bool cov = ( wl & lanebit ) != 0u; // covered (main.cpp:492-514) and live (:520)
-				if( COUNT )
-				{
-					nlive += cov ? 1u : 0u;
-					if( visit_hist && lane == 0 )
-					{
-						atomicAdd( &g_visit_hist[0][__popc( wl )], 1ull );
-						unsigned tl = 0;
+				const float avx0 = xmul( q1.x, vx0 ), avx1 = xmul( q1.x, vx1 );
+				const float bvx0 = xmul( q0.z, vx0 ), bvx1 = xmul( q0.z, vx1 );
+				const f32x2 bd = pack2( q0.z, q0.w ), cgb = pack2( q1.z, q1.w ); // packed multiplies: see xmul2
 #pragma unroll
-						for( int jj = 0; jj < 8; jj++ )
-							tl += __popc( live[jj] );
-						atomicAdd( &g_visit_hist[1][min( 32u, ( tl + 7u ) / 8u )], 1ull );
-					}
+				for( int j = 0; j < 8; j++ )
+				{
+					const unsigned wl = wd[j] & live[j];
+					if( wl == 0u ) // warp-uniform: no covered live pixel in this 8x4 block
+						continue;
+					if( COUNT )
+						nlive += count_visit( wl, lanebit, live, visit_hist, lane, g_visit_hist );
+					const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
+					const float vy = xsub( fpyr[j >> 1], q0.y );
+					// d2 = dot( v, inv_cov * v ), main.cpp:526 (inv_cov[0][1] == inv_cov[1][0] == b)
+					float bvy, dvy, vxrx, vyry;
+					unpack2( xmul2( bd, pack2( vy, vy ) ), bvy, dvy );
+					const float rx = xadd( avx, bvy );
+					const float ry = xadd( bvx, dvy );
+					unpack2( xmul2( pack2( vx, vy ), pack2( rx, ry ) ), vxrx, vyry );
+					const float d2 = xadd( vxrx, vyry );
+					// exp_approx( -0.5f * d2 ), main.cpp:49-83 (see gauss_of_d2), and alpha, main.cpp:527
+					const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
+					const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
+					// alpha = ( cov && !( t < threshold ) ) ? t8 * op : 0 with the two conditions folded into one predicate
+					const float alpha = select_alpha( wl & lanebit, t, xmul( t8, op ) );
+					float tga, tba;
+					unpack2( xmul2( xmul2( pack2( T[j], T[j] ), cgb ), pack2( alpha, alpha ) ), tga, tba );
+					Cr[j] = xadd( Cr[j], xmul( xmul( T[j], q1.y ), alpha ) );   // main.cpp:529-531
+					Cg[j] = xadd( Cg[j], tga );
+					Cb[j] = xadd( Cb[j], tba );
+					T[j] = xmul( T[j], xsub( 1.0f, alpha ) );                   // main.cpp:533
+					live[j] = __ballot_sync( 0xffffffffu, !( T[j] < min_T ) );
 				}
-				const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
-				const float vy = xsub( fpyr[j >> 1], q0.y );
-				// d2 = dot( v, inv_cov * v ), main.cpp:526 (inv_cov[0][1] == inv_cov[1][0] == b)
-				float bvy, dvy, vxrx, vyry;
-				unpack2( xmul2( bd, pack2( vy, vy ) ), bvy, dvy );
-				const float rx = xadd( avx, bvy );
-				const float ry = xadd( bvx, dvy );
-				unpack2( xmul2( pack2( vx, vy ), pack2( rx, ry ) ), vxrx, vyry );
-				const float d2 = xadd( vxrx, vyry );
-				// exp_approx( -0.5f * d2 ), main.cpp:49-83 (see gauss_of_d2), and alpha, main.cpp:527
-				const float t = __fmaf_rn( d2, -0.0625f, 1.0f );
-				const float t2 = xmul( t, t ), t4 = xmul( t2, t2 ), t8 = xmul( t4, t4 );
-				// alpha = ( cov && !( t < threshold ) ) ? t8 * op : 0 with the two conditions folded into one predicate
-				const float alpha = select_alpha( wl & lanebit, t, xmul( t8, op ) );
-				float tga, tba;
-				unpack2( xmul2( xmul2( pack2( T[j], T[j] ), cgb ), pack2( alpha, alpha ) ), tga, tba );
-				Cr[j] = xadd( Cr[j], xmul( xmul( T[j], q1.y ), alpha ) );   // main.cpp:529-531
-				Cg[j] = xadd( Cg[j], tga );
-				Cb[j] = xadd( Cb[j], tba );
-				T[j] = xmul( T[j], xsub( 1.0f, alpha ) );                   // main.cpp:533
-				live[j] = __ballot_sync( 0xffffffffu, !( T[j] < min_T ) );
+			}
+			else
+			{
+				// s (1 - d2/16) = ( s + A vx^2 ) + vy ( B vx + D vy ), A B D pre-scaled (SplatRec); per entry and block
+				// column: B vx and s + A vx^2
+				const float bvx0 = __fmul_rn( q0.z, vx0 ), bvx1 = __fmul_rn( q0.z, vx1 );
+				const float axx0 = __fmaf_rn( __fmul_rn( q1.x, vx0 ), vx0, op );
+				const float axx1 = __fmaf_rn( __fmul_rn( q1.x, vx1 ), vx1, op );
+#pragma unroll
+				for( int j = 0; j < 8; j++ )
+				{
+					const unsigned wl = wd[j] & live[j];
+					if( wl == 0u ) // warp-uniform: no covered live pixel in this 8x4 block
+						continue;
+					if( COUNT )
+						nlive += count_visit( wl, lanebit, live, visit_hist, lane, g_visit_hist );
+					const float vy = xsub( fpyr[j >> 1], q0.y );
+					const float alpha = relaxed_alpha( wl & lanebit, vy, q0.w, ( j & 1 ) ? bvx1 : bvx0, ( j & 1 ) ? axx1 : axx0 );
+					const float ta = __fmul_rn( T[j], alpha );
+					Cr[j] = __fmaf_rn( ta, q1.y, Cr[j] );                       // main.cpp:529-531
+					Cg[j] = __fmaf_rn( ta, q1.z, Cg[j] );
+					Cb[j] = __fmaf_rn( ta, q1.w, Cb[j] );
+					T[j] = __fsub_rn( T[j], ta );                               // main.cpp:533
+					live[j] = __ballot_sync( 0xffffffffu, !( T[j] < min_T ) );
+				}
 			}
 		}
 		unsigned anylive = 0;
@@ -223,10 +250,41 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 // both PDL blend kernels ask for the same shared-memory carveout, so that warps of the two grids can share an SM
 void prepare_forward_pdl()
 {
-	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
-	                      cudaSharedmemCarveoutMaxShared );
-	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
-	                      cudaSharedmemCarveoutMaxShared );
+#define CARVE( COUNT, EXACT )                                                                                         \
+	cudaFuncSetAttribute( k_forward<GS2D_FWD_MINB_DEFAULT, COUNT, true, EXACT>,                                      \
+	                      cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared )
+	CARVE( false, false );
+	CARVE( true, false );
+	CARVE( false, true );
+	CARVE( true, true );
+#undef CARVE
+}
+
+template <int MINB, bool COUNT, bool PDL, bool EXACT>
+static void launch_forward_as( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, int vh, cudaStream_t s )
+{
+	k_forward<MINB, COUNT, PDL, EXACT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image,
+	                                                       b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state,
+	                                                       COUNT ? vh : 0, PDL ? b.tile_done : nullptr, b.rowtab, b.rowrec );
+}
+template <int MINB, bool PDL>
+static void launch_forward_minb( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, bool count_live,
+                                 bool exact, int vh, cudaStream_t s )
+{
+	if( count_live )
+	{
+		if( exact )
+			launch_forward_as<MINB, true, PDL, true>( grid, g, b, sorted_buf, vh, s );
+		else
+			launch_forward_as<MINB, true, PDL, false>( grid, g, b, sorted_buf, vh, s );
+	}
+	else
+	{
+		if( exact )
+			launch_forward_as<MINB, false, PDL, true>( grid, g, b, sorted_buf, vh, s );
+		else
+			launch_forward_as<MINB, false, PDL, false>( grid, g, b, sorted_buf, vh, s );
+	}
 }
 
 int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool count_live, cudaStream_t s, bool pdl )
@@ -237,40 +295,18 @@ int launch_forward( const Geometry& g, const Buffers& b, int sorted_buf, bool co
 		return 0;
 	dim3 grid( g.tiles_x, rows, g.n_images );
 	const int vh = gs2d_tune( "GS2D_VISIT_HIST", 0 );
+	const bool exact = gs2d_exact_mode();
 	if( pdl ) // only the default register cap (32 warps per SM) has PDL twins: gs2d_pdl_usable()
 	{
 		cudaMemsetAsync( b.tile_done, 0, sizeof( unsigned ) * (size_t)g.n_tiles_total, s );
-		if( count_live )
-			k_forward<GS2D_FWD_MINB_DEFAULT, true, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
-			                                                                   b.target, b.image, b.cover, b.loss_partial,
-			                                                                   b.live_slots, b.staged_slots, b.state, vh,
-			                                                                   b.tile_done );
-		else
-			k_forward<GS2D_FWD_MINB_DEFAULT, false, true><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
-			                                                                    b.target, b.image, b.cover, b.loss_partial,
-			                                                                    b.live_slots, b.staged_slots, b.state, 0,
-			                                                                    b.tile_done );
+		launch_forward_minb<GS2D_FWD_MINB_DEFAULT, true>( grid, g, b, sorted_buf, count_live, exact, vh, s );
 		return 1;
 	}
-#define LAUNCH_FWD( MINB )                                                                                            \
-	do                                                                                                                \
-	{                                                                                                                 \
-		if( count_live )                                                                                              \
-			k_forward<MINB, true, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,   \
-			                                                  b.image, b.cover, b.loss_partial, b.live_slots,         \
-			                                                  b.staged_slots, b.state, vh, nullptr );                 \
-		else                                                                                                          \
-			k_forward<MINB, false, false><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target,  \
-			                                                   b.image, b.cover, b.loss_partial, b.live_slots,        \
-			                                                   b.staged_slots, b.state, 0, nullptr );                 \
-	} while( 0 )
 	switch( gs2d_tune( "GS2D_FWD_MINB", GS2D_FWD_MINB_DEFAULT ) )
 	{
-	case 24: LAUNCH_FWD( 24 ); break;
-	case 20: LAUNCH_FWD( 20 ); break;
-	default: LAUNCH_FWD( 32 ); break;
+	case 24: launch_forward_minb<24, false>( grid, g, b, sorted_buf, count_live, exact, vh, s ); break;
+	default: launch_forward_minb<32, false>( grid, g, b, sorted_buf, count_live, exact, vh, s ); break;
 	}
-#undef LAUNCH_FWD
 	return 1;
 }
 

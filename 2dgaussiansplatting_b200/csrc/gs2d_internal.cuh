@@ -5,9 +5,8 @@
 //       reference's Splat (main.cpp:85-93): pos.x pos.y sx sy rot color.r color.g color.b opacity.
 //       n_total = n_images * n_splats; global splat index g = image * n_splats + i.
 //   rec      : one 64-byte record per splat, rewritten every iteration by k_preprocess (SplatRec below)
-//   rect     : tile rectangle of the splat inside this rank's band (4 x u16), cnt: number of tiles in it
-//   keys/vals: (tile id, splat index) list entries, double-buffered for the LSD radix passes
-//   tile_range: [start,end) of every tile's list after the sort
+//   bucket_cnt / bucket_slots / bucket_off / triples / vals: the sort-free binning of gs2d_binning.cu (see Buffers)
+//   tile_range: [start,end) of every tile's list, ordered by splat index
 //   target / image : RGBA float32, row-major, n_images * H * W float4 (== pr::Image2DRGBA32, prp.cpp:751-756)
 #pragma once
 
@@ -37,18 +36,44 @@ enum
 	PL_OP
 };
 
-// 64-byte per-splat record (4 x float4). q0..q2 are what the forward pass reads; q3 holds the per-splat
-// invariants hoisted out of the backward pass (cos, sin, sx^-3, sy^-3, (sx^2-sy^2)/(sx^2 sy^2)).
+// 64-byte per-splat record (4 x float4), rewritten every iteration by k_preprocess. q0..q2 are what the forward pass
+// reads; q3 holds the per-splat invariants hoisted out of the backward pass (cos, sin, sx^-3, sy^-3,
+// (sx^2-sy^2)/(sx^2 sy^2)).
+// Two flavours of (A, B, D, op), chosen by the arithmetic mode of the context (GS2D_EXACT, gs2d_blend.cuh):
+//   exact   : A, B, D = inv_cov[0][0], inv_cov[1][0], inv_cov[1][1] (a, b, d) and op = opacity: the blend kernels
+//             evaluate d2, exp_approx and alpha operation for operation like main.cpp:526-533, never contracted;
+//   relaxed : with s = opacity^(1/8):  A = -s*a/16, B = -s*b/8, D = -s*d/16, op = s, so that
+//             s * (1 - d2/16) = (s + A vx^2) + vy (B vx + D vy)   [two FMAs per pixel]  and  alpha = (that)^8.
 struct __align__( 16 ) SplatRec
 {
-	float px, py, b, d;        // q0: position, inv_cov[1][0] (== inv_cov[0][1]), inv_cov[1][1]; (b, d) and (cg, cb) sit
-	float a, cr, cg, cb;       // q1: inv_cov[0][0], colour                      in aligned register pairs (xmul2)
-	float op;                  // q2: opacity
-	int begY, endY;            //     row range, main.cpp:490-491 (x86 truncation semantics)
+	float px, py, B, D;        // q0: position; (B, D) and (cg, cb) sit in aligned register pairs (xmul2)
+	float A, cr, cg, cb;       // q1
+	float op;                  // q2: opacity (exact) / opacity^(1/8) (relaxed)
+	unsigned idx;              //     global splat index (row table / RowRec lookup while the coverage words are built)
+	unsigned flags;            //     bit 0: the splat's rows are in the row table (SPLAT_IN_TABLE)
 	float rotc;                //     (sx^2 - sy^2) / (sx^2 sy^2)
 	float cosT, sinT, isx3, isy3; // q3
 };
 static_assert( sizeof( SplatRec ) == 64, "SplatRec must be 64 bytes" );
+#define SPLAT_IN_TABLE 1u
+
+// What the exact scan-line footprint needs (main.cpp:489-509), always unscaled; written by k_preprocess for every
+// splat, read by k_row_table (every splat of the band) and by the blend's in-kernel fallback (splats too tall for the
+// row table only).
+struct __align__( 16 ) RowRec
+{
+	float px, py, a, b;
+	float d;
+	int begY, endY;   // row range, main.cpp:490-491 (x86 truncation semantics)
+	unsigned tyr;     // first | last << 16 tile row of the splat inside this rank's band whose rows go into the row
+	                  // table; ROWREC_NONE: no tile, or too tall for the table (more than GS2D_ROWTAB_TILE_ROWS tile rows)
+};
+static_assert( sizeof( RowRec ) == 32, "RowRec must be 32 bytes" );
+#define ROWREC_NONE 0xffffffffu
+// Row table: per splat a ring of GS2D_ROWTAB_TILE_ROWS blocks of 16 packed row spans (pack_row_span), block of tile
+// row ty at ring position ty % GS2D_ROWTAB_TILE_ROWS: 512 bytes per splat, 64 contiguous bytes per (splat, tile row).
+#define GS2D_ROWTAB_TILE_ROWS 8
+#define GS2D_ROWTAB_STRIDE ( GS2D_ROWTAB_TILE_ROWS * GS2D_TILE )
 
 // Loop-carried scalars + flags, one per context, lives in device memory so that gs2d_step can be fully async.
 struct DevState
@@ -60,7 +85,14 @@ struct DevState
 	unsigned long long need_capacity; // != 0: the key buffers were too small; the iteration was skipped
 	int mse_slot;              // next slot of the mse ring written by k_finalize
 	int peer_fault;            // a peer-memory barrier timed out (a rank died or the call sequences diverged)
+	// The reference abort()s in the iteration whose Adam step produced a non-finite parameter (main.cpp:752-785), after
+	// the whole update loop and before that iteration's mse line. Mirror: k_advance of the NEXT iteration sees
+	// `nonfinite`, sets `frozen` and returns; from then on k_advance / k_adam are no-ops, so `iteration` stays at the
+	// failing iteration's index + 1 and the parameters are the ones the reference held when it aborted.
+	int frozen;
+	int pad_;
 };
+static_assert( sizeof( DevState ) == 48, "DevState is copied as 12 words (k_publish) and mirrored by the host" );
 
 struct Geometry
 {
@@ -104,6 +136,8 @@ struct Buffers
 	float* adam_m;  // [9][n_pad]
 	float* adam_v;  // [9][n_pad]
 	SplatRec* rec;  // [n_total]
+	RowRec* rowrec; // [n_total]
+	unsigned* rowtab; // [n_total][GS2D_ROWTAB_STRIDE] packed row spans (k_row_table -> k_forward)
 	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
 	unsigned short* bucket_slots; // [n_slices][nt_pad][GS2D_BUCKET_SLOTS] first arrivals of every bucket (slot binning)
 	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
@@ -129,8 +163,17 @@ struct Buffers
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
 // use_slots: slot binning unless the context has switched it off for now (gs2d_ctx::slot_binning) or GS2D_SLOTS=0
+// side: a second stream the row table kernel runs on, concurrently with the scan / place / rank kernels (fork and
+// join through ev_fork / ev_join; also inside a stream capture); nullptr: everything on s
+struct SideStream
+{
+	cudaStream_t stream;
+	cudaEvent_t ev_fork, ev_join;
+};
 int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_buf, cudaStream_t s,
-                               cudaEvent_t after_emit, bool use_slots );
+                               cudaEvent_t after_emit, bool use_slots, const SideStream* side );
+// arithmetic mode of the blend kernels: GS2D_EXACT (default 0 = relaxed: FMA contraction + folded opacity)
+bool gs2d_exact_mode();
 // developer tuning knob: integer environment variable read once per name, else the default
 int gs2d_tune( const char* env_name, int dflt );
 // pdl: forward/backward overlap through programmatic dependent launch (gs2d_blend.cuh); must be set for both or none,

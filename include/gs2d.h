@@ -130,7 +130,7 @@ int gs2d_download_state( gs2d_ctx* ctx, int image, gs2d_splat* splats, gs2d_spla
 int gs2d_set_optimize_opacity( gs2d_ctx* ctx, int enabled ); /* the ImGui checkbox, main.cpp:825 */
 int gs2d_get_optimize_opacity( const gs2d_ctx* ctx, int* enabled );
 
-/* n_iters full iterations (bin+sort, forward, backward, [allreduce], Adam), main.cpp:414-809.
+/* n_iters full iterations (binning, forward, backward, [gradient exchange], Adam), main.cpp:414-809.
  * mse: NULL => enqueue only (asynchronous); else n_iters*n_images doubles, mse[it*n_images+img] = the value the
  * reference prints at main.cpp:807 (render made with the pre-update parameters), and the call blocks. */
 int gs2d_step( gs2d_ctx* ctx, int n_iters, double* mse );
