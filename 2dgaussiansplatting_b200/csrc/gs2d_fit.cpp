@@ -29,7 +29,9 @@ static void usage()
 	fprintf( stderr,
 	         "usage: gs2d_fit <target.jpg|target.ppm> [--splats N=1024] [--iters K=300] [--device D=0]\n"
 	         "                [--opacity-from ITER] [--restart-at ITER] [--load ckpt] [--save ckpt]\n"
-	         "                [--out render.ppm] [--overlay overlay.csv] [--print-every M=1]\n" );
+	         "                [--out render.ppm] [--overlay overlay.csv] [--print-every M=1] [--exact]\n"
+	         "  --exact: the blend kernels keep the reference's operand order without FMA contraction (image bit-identical\n"
+	         "           to the CPU reference; default: relaxed arithmetic, results within FP32 round-off of it)\n" );
 }
 
 #define CHECK( call )                                                                                                 \
@@ -75,6 +77,8 @@ int main( int argc, char** argv )
 			out = v;
 		else if( a == "--overlay" && ( v = val() ) )
 			overlay = v;
+		else if( a == "--exact" )
+			gs2d_set_tuning( "GS2D_EXACT", 1 );
 		else if( a[0] != '-' && !target )
 			target = argv[i];
 		else

@@ -1,22 +1,27 @@
 #!/usr/bin/env python
 """bench.py — fit iterations/s (forward + backward + Adam) of the B200-native 2D Gaussian-splatting engine.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size 4096] [--splats 1000000]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c3|c4|c5]
 
-Workload (BASELINE.json metric / configs[2]): synthetic 4096x4096 RGB target, 1 M Gaussians initialised with the
-reference's own init() formula (main.cpp:280-305), lr 0.05, opacity not optimised. One "step" = one whole loop body of
-the reference (main.cpp:414-809): bin + sort, forward blend, loss, backward, [gradient all-reduce], Adam + clamps.
-N > 1 (launched by torchrun, one process per GPU): the image is split into tile-row bands, one per rank, and the
-per-Gaussian gradients are all-reduced over NCCL before Adam -> the total work is fixed ("strong" scaling).
+Workload (default c3 = BASELINE.json metric / configs[2]): synthetic 4096x4096 RGB target, 1 M Gaussians initialised
+with the reference's own init() formula (main.cpp:280-305), lr 0.05, opacity not optimised. One "step" = one whole
+loop body of the reference (main.cpp:414-809): binning, forward blend, loss, backward, [gradient exchange], Adam +
+clamps. N > 1 (launched by torchrun, one process per GPU): the image is split into tile-row bands, one per rank, and
+the per-Gaussian gradients are exchanged before Adam -> the total work is fixed ("strong" scaling).
+--config c4: 8192^2 / 4 M Gaussians (configs[3]); --config c5: 256 independent 512^2 images with 16 K Gaussians each
+(configs[4]; N > 1 = replicas only, 256 / N images per rank, no collective).
 
-Prints ONE JSON line (rank 0). `value` = device-timed iterations/s with all inputs resident in HBM; `e2e` = the same
-metric through the C ABI with HOST buffers: every step uploads the RGBA8 target from pinned host memory
-(gs2d_set_target_rgba8, the reference's own ingest format, prp.cpp:179-193 + :796-807) and reads the mse back.
+Prints ONE JSON line (rank 0). `value` = device-timed iterations/s with all inputs resident in HBM, profiling OFF (the
+iteration runs as the library runs it for a user: one CUDA graph per iteration on one GPU); the per-kernel-group times
+the roofline explains itself with come from separate, untimed passes over the same iterations. `e2e` = the same metric
+through the C ABI with HOST buffers: every step uploads the RGBA8 target from pinned host memory
+(gs2d_set_target_rgba8_async, the reference's own ingest format, prp.cpp:179-193 + :796-807) and reads the mse back.
 
 --impl reference: the reference's own CPU implementation of the path, single thread (the reference is
-single-threaded), on the box's host cores. oracle/_ref/ref_main (the unmodified main.cpp) is hard-wired to one JPEG
-and 1024 splats, so at this size the function-ised restatement oracle/gs2d_oracle.c is timed (bit-identical to
-main.cpp, tests/test_oracle.py); each step is a bounded sample (1/16 of the workload at equal density).
+single-threaded: main.cpp never calls prlib's ParallelFor / ThreadPool), on the box's host cores, on the SAME config:
+every warm-up and timed step is one real iteration of the full problem (4096^2 / 1 M: ~12 s each).
+oracle/_ref/ref_main (the unmodified main.cpp) is hard-wired to one JPEG and 1024 splats, so the function-ised
+restatement oracle/gs2d_oracle.c is timed (bit-identical to main.cpp, tests/test_oracle.py).
 """
 import argparse
 import importlib
@@ -34,7 +39,13 @@ sys.path.insert(0, ROOT)
 FLOP_FWD, FLOP_BWD = 27.0, 86.0  # per live (pixel, splat) pair, hoisted counts of SURVEY.md §8(d)
 ADAM_BYTES = 288.0               # per Gaussian: 8 planes x (p,g,m,v read + p,m,v,g write) + opacity plane p,g rw
 BIN_BYTES_PER_KEY = 13.0         # scan + rank passes per (tile, Gaussian) list entry, see run_ours
-SAMPLE_DIV = 16                  # CPU sample = 1/16 of the workload (same Gaussian density)
+
+CONFIGS = {
+    # name: (image side, Gaussians per image, images, BASELINE.json configs[] index)
+    "c3": (4096, 1_000_000, 1, 2),
+    "c4": (8192, 4_000_000, 1, 3),
+    "c5": (512, 16_384, 256, 4),
+}
 
 
 def measured_peaks():
@@ -97,25 +108,31 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_sample(size, splats, iters):
-    """Time the CPU oracle (the reference's algorithm, 1 thread) on 1/SAMPLE_DIV of the workload at equal density.
-    Returns (equivalent full-workload it/s, description, seconds per sample iteration)."""
+def oracle_state(args):
+    """The CPU oracle's loop-carried state and target for this config (one image: the reference fits one image)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
 
     gs2d = importlib.import_module("2dgaussiansplatting_b200")
-    side = int(round(size / SAMPLE_DIV ** 0.5))
-    n = max(1, splats // SAMPLE_DIV)
-    target = gs2d.synth_target(side, side, seed=1)
-    st = ob.State(side, side, n)
-    st.step(target)  # page in
+    target = np.rint(gs2d.synth_target(args.size, args.size, seed=1) * 255.0).astype(np.float32) / np.float32(255.0)
+    return ob.State(args.size, args.size, args.splats), np.ascontiguousarray(target.astype(np.float32))
+
+
+def cpu_sample(args, iters):
+    """Time the CPU oracle (the reference's algorithm, 1 thread) on REAL iterations of this config (for c5: of one of
+    the 256 images). Returns (equivalent whole-workload it/s, description)."""
+    st, target = oracle_state(args)
     t0 = time.perf_counter()
     for _ in range(iters):
         st.step(target)
     dt = (time.perf_counter() - t0) / iters
-    desc = (f"{iters} iterations of a {side}x{side} window with {n} Gaussians (1/{SAMPLE_DIV} of the workload at equal "
-            f"density, {dt:.2f} s each); value = sample it/s / {SAMPLE_DIV}")
-    return 1.0 / (dt * SAMPLE_DIV), desc, dt
+    if args.images > 1:
+        desc = (f"{iters} iterations of ONE of the {args.images} images ({args.size}x{args.size}, {args.splats} Gaussians, "
+                f"{dt:.3f} s each); value = 1 / ({args.images} x that): the images are independent")
+        return 1.0 / (dt * args.images), desc
+    desc = (f"{iters} real iterations of the full workload ({args.size}x{args.size}, {args.splats} Gaussians, "
+            f"{dt:.2f} s each, from init(); no extrapolation)")
+    return 1.0 / dt, desc
 
 
 def run_reference(args):
@@ -123,29 +140,28 @@ def run_reference(args):
     if rank != 0:
         return 0
     t_first = time.perf_counter()
-    # warm-up steps and timed steps are both sample iterations
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_binding as ob
-
-    gs2d = importlib.import_module("2dgaussiansplatting_b200")
-    side = int(round(args.size / SAMPLE_DIV ** 0.5))
-    n = max(1, args.splats // SAMPLE_DIV)
-    target = gs2d.synth_target(side, side, seed=1)
-    st = ob.State(side, side, n)
+    st, target = oracle_state(args)
+    # every warm-up and every timed step is one real iteration of the full problem (c5: of all its images in turn
+    # would take 256 x as long - there the step is one image and the value is divided, stated in `sample`)
     for _ in range(args.warmup):
         st.step(target)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         st.step(target)
     dt = (time.perf_counter() - t0) / max(args.steps, 1)
-    value = 1.0 / (dt * SAMPLE_DIV)
-    sample = (f"each step = one iteration of a {side}x{side} window with {n} Gaussians (1/{SAMPLE_DIV} of the "
-              f"workload at equal density, {dt:.2f} s); value = sample it/s / {SAMPLE_DIV}")
+    per_step = dt * args.images
+    value = 1.0 / per_step
+    if args.images > 1:
+        sample = (f"each step = one iteration of ONE of the {args.images} independent images ({dt:.3f} s); "
+                  f"ms_per_step and value are scaled by {args.images}")
+    else:
+        sample = (f"each step = one real iteration of the full {args.size}x{args.size} / {args.splats}-Gaussian problem "
+                  f"({dt:.2f} s), continuing the fit from init(); nothing extrapolated")
     line = {
         "impl": "reference", "metric": "fit_iters_per_sec", "value": value, "unit": "it/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * SAMPLE_DIV * 1e3, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "strong" if args.images == 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1, None),
         "cpu_baseline": {"value": value, "unit": "it/s", "cores": 1, "kind": "port", "sample": sample,
                          "host_cores_available": os.cpu_count()},
         "e2e": {"value": value, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -155,13 +171,29 @@ def run_reference(args):
     return 0
 
 
-def workload_config(args, n_gpus):
+def workload_config(args, n_gpus, comm_mode):
+    """comm_mode: (n_ranks, peer_memory) as gs2d_comm_mode reports it for the context that ran, or None."""
+    if n_gpus == 1:
+        par = "single GPU"
+    elif args.images > 1:
+        par = f"{n_gpus} replicas x {args.images // n_gpus} independent images, no collective"
+    elif comm_mode is not None and comm_mode[1]:
+        par = (f"{n_gpus} tile-row bands; gradient exchange = ONE fused kernel per rank over NVLink peer memory (CUDA "
+               f"IPC): reduce-scatter of the 9 gradient planes + Adam on the owned slice + all-gather of the "
+               f"parameters; flag barriers over peer mailboxes; NCCL only for the rendezvous (gs2d_comm_mode: peer_memory=1)")
+    else:
+        par = (f"{n_gpus} tile-row bands; gradient exchange = ncclAllReduce of the 9 gradient planes + the loss, Adam "
+               f"replicated (gs2d_comm_mode: peer_memory=0)")
+    img = f"{args.images} x " if args.images > 1 else ""
     return {
-        "workload": f"synthetic {args.size}x{args.size} RGB target, {args.splats} Gaussians (BASELINE configs[2])",
-        "image": [args.size, args.size], "n_gaussians": args.splats, "init": "reference init() main.cpp:280-305",
-        "optimize_opacity": False, "lr": 0.05,
-        "parallelism": "single GPU" if n_gpus == 1 else f"{n_gpus} tile-row bands + NCCL all-reduce of 9 gradient planes",
-        "l2_policy": "no flush: per-iteration inputs (target 268 MB, image 268 MB, key lists >250 MB) exceed the 126 MB L2",
+        "workload": f"synthetic {img}{args.size}x{args.size} RGB target, {args.splats} Gaussians"
+                    f"{' each' if args.images > 1 else ''} (BASELINE configs[{CONFIGS[args.config][3]}])",
+        "image": [args.size, args.size], "n_gaussians": args.splats, "n_images": args.images,
+        "init": "reference init() main.cpp:280-305", "optimize_opacity": False, "lr": 0.05, "parallelism": par,
+        "arithmetic": "relaxed (GS2D_EXACT=0, the library default: FMA-contracted blend chain, results within FP32 "
+                      "round-off of the reference; `exact_mode` in this line = the bit-exact kernels)",
+        "l2_policy": "no flush: per-iteration inputs (target + image 2 x 268 MB, row table 512 MB, key lists >250 MB at "
+                     "c3) exceed the 126 MB L2",
     }
 
 
@@ -184,17 +216,35 @@ def run_ours(args):
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    S, N, K, W = args.size, args.splats, args.steps, args.warmup
-    target = gs2d.synth_target(S, S, seed=1)
-    pinned_u8 = torch.empty((S, S, 4), dtype=torch.uint8, pin_memory=True)
-    pinned_u8.numpy()[...] = np.rint(target * 255.0).astype(np.uint8)  # 8-bit target, as a decoded JPEG would be
+    S, N, K, W = args.size, args.splats, args.steps, max(args.warmup, 3)
+    replicas = args.images > 1          # c5: independent images, replicas only
+    n_img = args.images // world if replicas else 1
+    if replicas and args.images % world:
+        raise SystemExit(f"--config c5: {args.images} images do not divide over {world} ranks")
+    img0 = rank * n_img if replicas else 0
+    # 8-bit targets, as a decoded JPEG would be; one pinned buffer per image of this rank
+    pinned = []
+    for i in range(n_img):
+        t = torch.empty((S, S, 4), dtype=torch.uint8, pin_memory=True)
+        t.numpy()[...] = np.rint(gs2d.synth_target(S, S, seed=1 + img0 + i) * 255.0).astype(np.uint8)
+        pinned.append(t)
 
-    fit = gs2d.Fitter(S, S, N, device=local_rank)
-    if world > 1:
+    fit = gs2d.Fitter(S, S, N, n_images=n_img, device=local_rank)
+    comm_mode = None
+    if world > 1 and not replicas:
         box = [gs2d.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         fit.comm_init(rank, world, box[0])
-    fit.set_target_u8_ptr(pinned_u8.data_ptr())
+        comm_mode = fit.comm_mode()
+        if os.environ.get("GS2D_PEER_ADAM", "1") != "0" and not comm_mode[1]:
+            print(f"[bench rank {rank}] WARNING: the peer-memory exchange was requested but not agreed (CUDA IPC / P2P "
+                  f"unavailable?): running the NCCL all-reduce path", file=sys.stderr)
+
+    def upload_all():
+        for i, t in enumerate(pinned):
+            fit.set_target_u8_ptr(t.data_ptr(), image=i)
+
+    upload_all()
     fit.restart()
 
     peaks = measured_peaks()
@@ -208,63 +258,84 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- counting pass (untimed): live (pixel, Gaussian) pairs and list entries of the SAME K iterations ---------
-    # The counting variant of the forward blend costs ~10 % (profiles/r1_ncu_blend_v4.txt), so the work counters the
-    # roofline needs are taken on an identical, untimed run of the same iterations and the timed run has them off.
-    fit.step(max(W, 3))  # warm-up (>= 3), also grows the key buffers to their steady size
-    fit.set_stats(True)
-    fit.set_profiling(True)  # resets the running sums
-    fit.step(K, want_mse=False)
-    fit.sync()
-    stats = fit.stats()
-    fit.set_profiling(False)
-    fit.set_stats(False)
-    fit.restart()
+    def timed_pass(profile=False, stats=False):
+        """restart + W warm-up iterations, then K iterations enqueued back to back behind ONE more untimed iteration
+        that is already running when they are enqueued: the CUDA events around the K iterations (on the library's
+        stream) then start at an iteration boundary with the device busy - and, with N ranks, behind that iteration's
+        device-side barrier, i.e. aligned across the ranks. Returns device ms for the K iterations."""
+        fit.restart()
+        fit.step(W - 1)
+        barrier()
+        if stats:
+            fit.set_stats(True)
+        if profile:
+            fit.set_profiling(True)  # resets the running sums; also keeps the iteration out of the CUDA graph
+        fit.step(1, want_mse=False)
+        fit.step(K, want_mse=False)
+        fit.sync()
+        ms = fit.last_step_ms()
+        out = {"ms": ms}
+        if profile:
+            prof, n_prof = fit.get_profile()
+            # K + 1 iterations were profiled (the aligning one included): means per iteration
+            out["prof"] = prof
+            fit.set_profiling(False)
+        if stats:
+            out["stats"] = fit.stats()
+            fit.set_stats(False)
+        barrier()
+        return out
 
-    # ---- device-resident run: `value` ---------------------------------------------------------------------------
-    fit.step(max(W, 3))
+    # ---- counting pass (untimed): live (pixel, Gaussian) pairs and list entries of the SAME iterations ------------
+    # The counting variant of the forward blend is slower, so the work counters the roofline needs are taken on an
+    # identical, untimed run of the same iterations and the timed run has them off.
+    fit.step(3)  # grows the key buffers to their steady size, builds the graph
+    cnt = timed_pass(profile=True, stats=True)
+    stats = cnt["stats"]
+
+    # ---- device-resident run: `value` (profiling off: the library's own launch path, graph replay on one GPU) -----
+    fit.restart()
+    fit.step(W - 1)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    fit.set_profiling(True)
+    fit.step(1, want_mse=False)
     launches0 = fit.launch_count()
     t0 = time.perf_counter()
     fit.step(K, want_mse=False)
     fit.sync()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    dev_ms = fit.last_step_ms()  # CUDA events on the library's stream around the K iterations
-    prof, n_prof = fit.get_profile()
-    fit.set_profiling(False)
+    dev_ms = fit.last_step_ms()  # CUDA events on the library's stream around exactly the K iterations
     clocks = sampler.stop()
     launches = fit.launch_count() - launches0
     barrier()
-    # ---- the same iterations once more with the forward -> backward overlap off (untimed for `value`) -----------
-    # In the timed run the backward grid starts inside the forward grid's tail (programmatic dependent launch,
-    # gs2d_blend.cuh), so CUDA events can only bracket the PAIR. The per-kernel durations the roofline explains
-    # itself with come from this pass: same fit, same iterations, the two grids serialised.
+
+    # ---- per-kernel-group times (untimed for `value`): the same iterations with CUDA events between the groups ----
+    prof = timed_pass(profile=True)["prof"]
+    # ... and once more with the forward -> backward overlap off: in the runs above the backward grid starts inside
+    # the forward grid's tail (programmatic dependent launch, gs2d_blend.cuh), so events can only bracket the PAIR
     gs2d.set_tuning("GS2D_PDL", 0)
-    fit.restart()
-    fit.step(max(W, 3))
-    fit.set_profiling(True)
-    fit.step(K, want_mse=False)
-    fit.sync()
-    sep_ms = fit.last_step_ms() / K
-    prof_sep, _ = fit.get_profile()
-    fit.set_profiling(False)
+    sep = timed_pass(profile=True)
+    prof_sep, sep_ms = sep["prof"], sep["ms"] / K
     gs2d.set_tuning("GS2D_PDL", 1)
-    barrier()
-    t = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device="cuda")
+    # ---- the bit-exact kernels (GS2D_EXACT=1), same iterations, for the record ------------------------------------
+    gs2d.set_tuning("GS2D_EXACT", 1)
+    exact_ms = timed_pass()["ms"]
+    exact_prof = timed_pass(profile=True)["prof"]
+    gs2d.set_tuning("GS2D_EXACT", 0)
+
+    t = torch.tensor([dev_ms, wall_ms, exact_ms], dtype=torch.float64, device="cuda")
     live = torch.tensor([float(stats["live_pairs_sum"]), float(stats["keys_sum"]), float(stats["n_forwards"])],
                         dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(live, op=dist.ReduceOp.SUM)
         live[2] /= world
-    dev_ms, wall_ms = float(t[0]), float(t[1])
+    dev_ms, wall_ms, exact_ms = float(t[0]), float(t[1]), float(t[2])
     ms_per_step = dev_ms / K
     value = 1e3 / ms_per_step
     n_fw = max(float(live[2]), 1.0)
-    live_per_it, keys_per_it = float(live[0]) / n_fw, float(live[1]) / n_fw
+    live_per_it, keys_per_it = float(live[0]) / n_fw, float(live[1]) / n_fw  # whole job (all ranks, all images)
 
     # ---- end to end through the C ABI with host buffers: `e2e` --------------------------------------------------
     # Every step copies its input (the RGBA8 target; this rank's band of it when sharded) from pinned host memory and
@@ -276,33 +347,39 @@ def run_ours(args):
     # Both loops run the SAME iterations of the fit as the device-resident pass (restart + the same warm-up): the
     # work per iteration drifts as the fit converges, so a pass over later iterations would not be comparable.
     Ke = max(3, min(K, args.e2e_steps)) if args.e2e_steps > 0 else K
-    h2d_bytes = fit.target_bytes_per_upload()
+    h2d_bytes = fit.target_bytes_per_upload() * n_img
+    e2e_ms = e2e_serial_ms = None
+    mse_last = None
+    if n_img == 1:
+        fit.restart()
+        fit.step(W)
+        fit.set_target_u8_ptr_async(pinned[0].data_ptr())  # pipeline fill: the target of the first timed step
+        barrier()
+        t0 = time.perf_counter()
+        prev = None
+        for _ in range(Ke):
+            fit.step(1, want_mse=False)                           # enqueue the step (its target was uploaded before)
+            ticket = fit.mse_ticket()                             # D2H of this step's result, enqueued behind it
+            fit.set_target_u8_ptr_async(pinned[0].data_ptr())     # H2D of the next step's input, overlapping this step
+            if prev is not None:
+                mse_last = fit.mse_wait(prev)                     # blocks on the PREVIOUS step's result only
+            prev = ticket
+        mse_last = fit.mse_wait(prev)
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / Ke
+    # the same without the overlap (blocking upload of every image, then the step with its loss read back); for the
+    # image batch (c5) this IS the end-to-end number: the asynchronous upload holds one image at a time
     fit.restart()
-    fit.step(max(W, 3))
-    fit.set_target_u8_ptr_async(pinned_u8.data_ptr())  # pipeline fill: the target of the first timed step
+    fit.step(W)
     barrier()
     t0 = time.perf_counter()
-    mse_last, prev = None, None
     for _ in range(Ke):
-        fit.step(1, want_mse=False)                         # enqueue the step (its target was uploaded before)
-        ticket = fit.mse_ticket()                           # D2H of this step's result, enqueued behind it
-        fit.set_target_u8_ptr_async(pinned_u8.data_ptr())   # H2D of the next step's input, overlapping this step
-        if prev is not None:
-            mse_last = fit.mse_wait(prev)                   # blocks on the PREVIOUS step's result only
-        prev = ticket
-    mse_last = fit.mse_wait(prev)
-    torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / Ke
-    # the same without the overlap (blocking upload, then the step), for the record
-    fit.restart()
-    fit.step(max(W, 3))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(Ke):
-        fit.set_target_u8_ptr(pinned_u8.data_ptr())
-        fit.step(1)
+        upload_all()
+        mse_last = fit.step(1)[0]
     torch.cuda.synchronize()
     e2e_serial_ms = (time.perf_counter() - t0) * 1e3 / Ke
+    if e2e_ms is None:
+        e2e_ms = e2e_serial_ms
     te = torch.tensor([e2e_ms, e2e_serial_ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -318,75 +395,90 @@ def run_ours(args):
     hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
     kern = {}
+    per_rank_live = live_per_it / world
+
+    def blend_entry(ms, flop, **kw):
+        a = flop * per_rank_live / (ms * 1e-3) / 1e12
+        return dict({"ms": ms, "bound": "fp32_issue", "achieved": a, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": a / fp32_peak}, **kw)
+
     blend_ms = prof["forward"] + prof["backward"]
     if blend_ms > 0:
-        # timed region: k_forward + k_backward overlapped (+ k_finalize_loss and two small memsets, ~15 us)
-        a = (FLOP_FWD + FLOP_BWD) * live_per_it / world / (blend_ms * 1e-3) / 1e12
-        kern["blend_overlapped"] = {"ms": blend_ms, "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
-                                    "unit": "TFLOP/s", "frac": a / fp32_peak,
-                                    "what": "k_forward + k_backward as launched in the timed region: the backward grid "
-                                            "fills the forward grid's tail (programmatic dependent launch), CUDA "
-                                            "events bracket the pair; 27 + 86 flop per live pair"}
+        kern["blend_overlapped"] = blend_entry(
+            blend_ms, FLOP_FWD + FLOP_BWD,
+            what="k_forward + k_backward as the library launches them: the backward grid fills the forward grid's "
+                 "tail (programmatic dependent launch), CUDA events bracket the pair; 27 + 86 flop per live pair. "
+                 "Measured in an untimed pass over the same iterations (events between the kernel groups keep the "
+                 "iteration out of the CUDA graph, so `value` is timed without them)")
     if prof_sep["forward"] > 0:
-        a = FLOP_FWD * live_per_it / world / (prof_sep["forward"] * 1e-3) / 1e12
-        kern["k_forward"] = {"ms": prof_sep["forward"], "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
-                             "unit": "TFLOP/s", "frac": a / fp32_peak, "pass": "serialised (GS2D_PDL=0), untimed"}
+        kern["k_forward"] = blend_entry(prof_sep["forward"], FLOP_FWD, **{"pass": "serialised (GS2D_PDL=0), untimed"})
     if prof_sep["backward"] > 0:
-        a = FLOP_BWD * live_per_it / world / (prof_sep["backward"] * 1e-3) / 1e12
-        kern["k_backward"] = {"ms": prof_sep["backward"], "bound": "fp32_issue", "achieved": a, "peak": fp32_peak,
-                              "unit": "TFLOP/s", "frac": a / fp32_peak, "pass": "serialised (GS2D_PDL=0), untimed"}
+        kern["k_backward"] = blend_entry(prof_sep["backward"], FLOP_BWD, **{"pass": "serialised (GS2D_PDL=0), untimed"})
+    eb = exact_prof["forward"] + exact_prof["backward"]
+    if eb > 0:
+        kern["blend_overlapped_exact_mode"] = blend_entry(eb, FLOP_FWD + FLOP_BWD, **{"pass": "GS2D_EXACT=1, untimed"})
     kern["serialised_ms_per_step"] = {"ms": sep_ms}
     if prof["sort"] > 0:
         # k_scan_* + k_place + k_rank with slot binning (gs2d_binning.cu): per bucket (3.4 entries) the 16-byte slot row,
         # the 2-byte counter twice (scan, k_rank), the 4-byte offset written and read = 30 B, i.e. 9 B per list entry,
-        # + 4 B per entry written in index order
+        # + 4 B per entry written in index order. k_row_table runs beside these kernels on a second stream.
         b = keys_per_it / world * BIN_BYTES_PER_KEY
         a = b / (prof["sort"] * 1e-3) / 1e9
         kern["place_rank"] = {"ms": prof["sort"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
                               "frac": a / hbm_peak, "bytes_per_list_entry": BIN_BYTES_PER_KEY}
     if prof["adam"] > 0:
-        a = ADAM_BYTES * N / (prof["adam"] * 1e-3) / 1e9
+        a = ADAM_BYTES * N * n_img / (prof["adam"] * 1e-3) / 1e9
         kern["k_adam"] = {"ms": prof["adam"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
                           "frac": a / hbm_peak}
     kern["preprocess_emit"] = {"ms": prof["preprocess_emit"]}
-    kern["allreduce"] = {"ms": prof["allreduce"]}
+    kern["exchange"] = {"ms": prof["allreduce"],
+                        "what": "barrier 1 + loss all-reduce (peer path) / gradient all-reduce (NCCL path)"}
     dom = max((k for k in kern if "frac" in kern[k] and "pass" not in kern[k]), key=lambda k: kern[k]["ms"])
-    traffic = None
+    traffic, traffic_src = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = tj["k_forward"] + tj["k_backward"] if dom == "blend_overlapped" else tj.get(dom)
+        if args.config == "c3" and world == 1:
+            traffic = tj["k_forward"] + tj["k_backward"] if dom == "blend_overlapped" else tj.get(dom)
+            traffic_src = tj.get("source")
     except Exception:
         pass
     roofline = {"kernel": dom, "bound": kern[dom]["bound"], "achieved": kern[dom]["achieved"], "peak": kern[dom]["peak"],
                 "unit": kern[dom]["unit"], "frac": kern[dom]["frac"], "traffic": traffic,
+                "traffic_source": traffic_src,
                 "peak_source": ("gs2d_microbench_fp32 on this device (FP32 FMA issue rate; MEASURED_PEAKS.json has no "
                                 "FP32 figure)") if kern[dom]["bound"] == "fp32_issue" else hbm_src,
                 "algorithmic_work": "27 (fwd) / 86 (bwd) flop per live (pixel,splat) pair x live pairs counted on the device; "
-                                    "traffic = dram bytes of both blend kernels per iteration (ncu, serialised capture)",
+                                    "traffic = dram bytes of both blend kernels per iteration from a committed ncu capture "
+                                    "(see traffic_source), not measured in this run",
                 "live_pairs_per_iteration": live_per_it, "keys_per_iteration": keys_per_it,
                 "hbm_copy_gbs_this_device": hbm_peak_local, "kernels": kern}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        v, desc, _ = cpu_sample(S, N, args.cpu_iters)
+        v, desc = cpu_sample(args, args.cpu_iters)
         cpu = {"value": v, "unit": "it/s", "cores": 1, "kind": "port", "sample": desc,
                "host_cores_available": os.cpu_count()}
 
     line = {
-        "metric": "fit_iters_per_sec", "value": value, "unit": "it/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+        "metric": "fit_iters_per_sec", "value": value, "unit": "it/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if replicas else "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world, comm_mode),
         "clocks": clocks, "wall_ms_per_step": wall_ms / K,
         "e2e": {"value": 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d_bytes * world,
-                "d2h_bytes_per_step": (8 + 40) * world, "ms_per_step": e2e_ms, "steps": Ke,
+                "d2h_bytes_per_step": (8 * n_img + 48) * world, "ms_per_step": e2e_ms, "steps": Ke,
                 "serial_ms_per_step": e2e_serial_ms,
                 "what": "per step and rank: gs2d_step(1) enqueued, gs2d_set_target_rgba8_async of the next step's "
                         "target from pinned host memory (this rank's band), gs2d_mse_ticket for this step (D2H of the "
-                        "loss and the 40-byte device state) and gs2d_mse_wait (blocking) for the previous one; "
+                        "loss and the 48-byte device state) and gs2d_mse_wait (blocking) for the previous one; "
                         "serial_ms_per_step = blocking gs2d_set_target_rgba8 then gs2d_step(1, &mse)"},
         "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "exact_mode": {"value": 1e3 * K / exact_ms, "unit": "it/s", "ms_per_step": exact_ms / K,
+                       "what": "GS2D_EXACT=1: blend kernels in the reference's operand order without FMA contraction "
+                               "(image bit-identical to the CPU reference); same iterations, device-timed like `value`"},
         "last_mse": float(mse_last[0]) if mse_last is not None else None,
     }
+    if replicas:
+        line["image_iters_per_sec"] = value * args.images
     _emit(line)
     fit.close()
     if dist is not None:
@@ -410,18 +502,24 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--size", type=int, default=4096)
-    ap.add_argument("--splats", type=int, default=1_000_000)
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS), help="BASELINE.json workload (default: the metric's)")
+    ap.add_argument("--size", type=int, default=0, help="override the image side (development)")
+    ap.add_argument("--splats", type=int, default=0, help="override the Gaussians per image (development)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end loops (0 = --steps)")
-    ap.add_argument("--cpu-iters", type=int, default=10)
+    ap.add_argument("--cpu-iters", type=int, default=0, help="iterations of the cpu_baseline sample (0 = per config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    side, n, images, _ = CONFIGS[args.config]
+    args.size = args.size or side
+    args.splats = args.splats or n
+    args.images = images
+    if args.cpu_iters <= 0:
+        # ~10-30 s of CPU work: c3 ~12 s per iteration, c4 ~50 s, c5 ~0.2 s per image-iteration
+        args.cpu_iters = {"c3": 2, "c4": 1, "c5": 20}[args.config]
     if args.impl == "reference":
-        if args.steps > 40:
-            args.steps = 40  # bounded: ~1 s per sample step on one core
         return run_reference(args)
     return run_ours(args)
 

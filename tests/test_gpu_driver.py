@@ -36,15 +36,21 @@ def test_driver_stdout_equals_reference_stdout(golden_dir, tmp_path):
     write_target_ppm(golden_dir, "c1", ppm)
     out_ppm = str(tmp_path / "render.ppm")
     csv = str(tmp_path / "overlay.csv")
-    r = subprocess.run([FIT, ppm, "--iters", "60", "--out", out_ppm, "--overlay", csv], capture_output=True, text=True,
-                       timeout=300)
-    assert r.returncode == 0, r.stderr
-    got = parse(r.stdout.strip().splitlines())
     ref = parse(open(os.path.join(golden_dir, "c1_mse.txt")).read().strip().splitlines()[:60])
-    assert [g[0] for g in got] == list(range(60))
-    assert r.stdout.splitlines()[0] == open(os.path.join(golden_dir, "c1_mse.txt")).readline().rstrip("\n")
-    rel = np.array([abs(g[1] - e[1]) / e[1] for g, e in zip(got, ref)])
-    assert rel[:50].max() < 1e-4 and rel.max() < 2e-3, rel.max()
+    # --exact: the reference's arithmetic, iteration 0 prints the very same line; default (relaxed arithmetic, FMA
+    # contraction): the same curve within FP32 round-off of the image (2e-6 on the first loss)
+    for extra in (["--exact"], []):
+        r = subprocess.run([FIT, ppm, "--iters", "60", "--out", out_ppm, "--overlay", csv] + extra, capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        got = parse(r.stdout.strip().splitlines())
+        assert [g[0] for g in got] == list(range(60))
+        rel = np.array([abs(g[1] - e[1]) / e[1] for g, e in zip(got, ref)])
+        if extra:
+            assert r.stdout.splitlines()[0] == open(os.path.join(golden_dir, "c1_mse.txt")).readline().rstrip("\n")
+        else:
+            assert rel[0] < 2e-6, rel[0]
+        assert rel[:50].max() < 1e-4 and rel.max() < 2e-3, rel.max()
     # the dumped render is the last iteration's image0 and the overlay has one row per splat
     img = gs2d.load_image(out_ppm)
     assert img.shape == (213, 268, 4) and img[..., :3].std() > 5

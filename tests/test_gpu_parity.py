@@ -23,6 +23,58 @@ pytestmark = pytest.mark.gpu
 
 IMG_ATOL = 1.0 / 256.0 * 1.01  # one flipped decision changes a pixel by at most T*alpha <= MIN_THROUGHPUT-ish
 GRAD_RTOL = 2e-4
+# Relaxed arithmetic (GS2D_EXACT=0, the library's default; gs2d_forward.cu): alpha = ( s (1 - d2/16) )^8 with FMA
+# contraction and s = opacity^(1/8) folded into the inverse covariance: ~3 ulp on the argument, x8 through the power
+# => alpha within ~2e-6 relative; colour = sum of <= ~100 such terms in [0, 1].
+RELAXED_IMG_TOL = 1e-5       # 99.99 % of the pixels; the rest is bounded by one flipped T < 1/256 decision (IMG_ATOL)
+RELAXED_GRAD_RTOL = 1e-3     # |dg| <= rtol * (|g| + mean|g|)
+MODES = ["exact", "relaxed"]
+
+
+@pytest.fixture(params=MODES)
+def mode(request):
+    """Run the test once per arithmetic mode of the blend kernels; the default (relaxed) is restored afterwards."""
+    gs2d.set_tuning("GS2D_EXACT", 1 if request.param == "exact" else 0)
+    yield request.param
+    gs2d.set_tuning("GS2D_EXACT", 0)
+
+
+@pytest.fixture
+def exact():
+    gs2d.set_tuning("GS2D_EXACT", 1)
+    yield
+    gs2d.set_tuning("GS2D_EXACT", 0)
+
+
+def grad_rtol(mode, exact_rtol=GRAD_RTOL):
+    return exact_rtol if mode == "exact" else max(exact_rtol, RELAXED_GRAD_RTOL)
+
+
+_libm = None
+
+
+def safe_rotations(rng, n, lo=-7.0, hi=7.0):
+    """Rotations whose glibc sinf / cosf (what the reference and the oracle call) are the correctly rounded values.
+    The device evaluates sincos in double and rounds once, i.e. it returns the correctly rounded float; this
+    container's glibc differs from that in the last bit for ~2.5 % of the arguments (sin or cos), and every such
+    Gaussian perturbs the alpha of all its pixels by ~1e-7 relative - THE reason the bit-identical fraction of an
+    image falls with the number of Gaussians per pixel (0.98 at 17 live per pixel, 0.90 at 80). With these rotations
+    the device and the oracle start from identical sin / cos and the image must be bit-identical almost everywhere."""
+    import ctypes
+
+    global _libm
+    if _libm is None:
+        _libm = ctypes.CDLL("libm.so.6")
+        for f in (_libm.sinf, _libm.cosf):
+            f.restype, f.argtypes = ctypes.c_float, [ctypes.c_float]
+    out = np.empty(0, np.float32)
+    while len(out) < n:
+        x = rng.uniform(lo, hi, 2 * n).astype(np.float32)
+        s = np.array([_libm.sinf(float(v)) for v in x], np.float32)
+        c = np.array([_libm.cosf(float(v)) for v in x], np.float32)
+        ok = (s == np.sin(x.astype(np.float64)).astype(np.float32)) & (c == np.cos(x.astype(np.float64)).astype(np.float32))
+        out = np.concatenate([out, x[ok]])
+    return out[:n]
 
 
 def load_target(golden_dir, cfg):
@@ -32,28 +84,33 @@ def load_target(golden_dir, cfg):
     return w, h, rgba8
 
 
-def random_splats(rng, W, H, n, smin=2.0, smax=24.0, opacity=(0.1, 1.0)):
+def random_splats(rng, W, H, n, smin=2.0, smax=24.0, opacity=(0.1, 1.0), safe_rot=False):
     s = np.zeros(n, ob.SPLAT_DTYPE)
     s["pos"][:, 0] = rng.uniform(-8, W + 8, n)
     s["pos"][:, 1] = rng.uniform(-8, H + 8, n)
     s["sx"] = rng.uniform(smin, smax, n)
     s["sy"] = rng.uniform(smin, smax, n)
-    s["rot"] = rng.uniform(-7, 7, n)
+    s["rot"] = safe_rotations(rng, n) if safe_rot else rng.uniform(-7, 7, n)
     s["color"] = rng.uniform(0, 1, (n, 3))
     s["opacity"] = rng.uniform(*opacity, n)
     return s
 
 
-def assert_image_close(img_gpu, img_cpu, min_exact=0.98):
-    """>= min_exact of the pixels bit-identical, >= 99.99 % within 4 ulp of 1.0 (a last-bit difference of cosf/sinf on
-    one of the covering splats), and nothing beyond one flipped coverage / liveness decision (IMG_ATOL)."""
+def assert_image_close(img_gpu, img_cpu, min_exact=0.98, mode="exact"):
+    """exact mode: >= min_exact of the pixels bit-identical, >= 99.99 % within 4 ulp of 1.0 (a last-bit difference of
+    cosf/sinf on one of the covering splats), and nothing beyond one flipped coverage / liveness decision (IMG_ATOL).
+    relaxed mode: >= 99.99 % within RELAXED_IMG_TOL, nothing beyond IMG_ATOL."""
     assert img_gpu.shape == img_cpu.shape
     assert (img_gpu[..., 3] == 1.0).all()  # w reset to 1, main.cpp:543-546
     same = (img_gpu[..., :3] == img_cpu[..., :3]).all(axis=2)
     diff = np.abs(img_gpu[..., :3] - img_cpu[..., :3]).max(axis=2)
     d = diff.max()
-    assert same.mean() >= min_exact, f"only {same.mean():.5f} of the pixels are bit-identical (max diff {d})"
-    assert (diff <= 5e-7).mean() >= 0.9999, (diff <= 5e-7).mean()
+    print(f"[{mode}] image: bit-identical {same.mean():.5f}, q99.99 {np.quantile(diff, 0.9999):.3e}, max {d:.3e}")
+    if mode == "exact":
+        assert same.mean() >= min_exact, f"only {same.mean():.5f} of the pixels are bit-identical (max diff {d})"
+        assert (diff <= 5e-7).mean() >= 0.9999, (diff <= 5e-7).mean()
+    else:
+        assert (diff <= RELAXED_IMG_TOL).mean() >= 0.9999, ((diff <= RELAXED_IMG_TOL).mean(), np.quantile(diff, 0.9999))
     assert d <= IMG_ATOL, d
     return same.mean(), d
 
@@ -65,6 +122,7 @@ def assert_grads_close(g_gpu, g_cpu, rtol=GRAD_RTOL):
         scale = np.abs(b).mean() + 1e-30
         err = np.abs(a - b) / (np.abs(b) + scale)
         worst = max(worst, err.max())
+        print(f"grad {f}: max rel err {err.max():.3e} (rtol {rtol:.1e})")
         assert err.max() <= rtol, f"{f}: max rel err {err.max():.3e} at {np.unravel_index(err.argmax(), err.shape)}"
     return worst
 
@@ -80,7 +138,7 @@ def test_init_matches_reference_init():
 
 
 @pytest.mark.parametrize("cfg", ["c1", "c2"])
-def test_forward_backward_reference_jpegs(golden_dir, cfg):
+def test_forward_backward_reference_jpegs(golden_dir, cfg, mode):
     W, H, rgba8 = load_target(golden_dir, cfg)
     target = ob.u8_to_target(rgba8)
     with gs2d.Fitter(W, H, 1024) as fit:
@@ -95,17 +153,24 @@ def test_forward_backward_reference_jpegs(golden_dir, cfg):
         assert fit.stats()["live_pairs_backward"] == stats["live_pairs"]  # both passes walk the same live set
     splats = ob.init_splats(W, H, 1024)
     img_cpu, visited, live = ob.forward(W, H, splats)
-    exact, d = assert_image_close(img, img_cpu)
+    exact, d = assert_image_close(img, img_cpu, mode=mode)
     if cfg == "c1":  # the committed render of the unmodified reference
         ref0 = np.load(os.path.join(golden_dir, "c1_image_itr0.npz"))["rgb"]
-        assert (img[..., :3] == ref0).all(axis=2).mean() >= 0.98
-    assert abs(mse - ob.mse(W, H, img_cpu, target)) <= 1e-9 * mse + 1e-6 * (1 - exact) * 65025
+        if mode == "exact":
+            assert (img[..., :3] == ref0).all(axis=2).mean() >= 0.98
+        else:
+            assert np.abs(img[..., :3] - ref0).max() <= RELAXED_IMG_TOL
+    mse_cpu = ob.mse(W, H, img_cpu, target)
+    if mode == "exact":
+        assert abs(mse - mse_cpu) <= 1e-9 * mse + 1e-6 * (1 - exact) * 65025
+    else:
+        assert abs(mse - mse_cpu) <= 2e-6 * mse_cpu, (mse, mse_cpu)
     assert abs(stats["live_pairs"] - live) <= 1e-4 * live  # same live set => same pair count
     g_cpu = ob.backward(W, H, splats, img_cpu, target)
-    assert_grads_close(g, g_cpu)
+    assert_grads_close(g, g_cpu, rtol=grad_rtol(mode))
 
 
-def test_loss_curve_matches_reference_stdout(golden_dir):
+def test_loss_curve_matches_reference_stdout(golden_dir, mode):
     """Free-running fit of the reference's default config against the mse lines the unmodified main.cpp printed."""
     W, H, rgba8 = load_target(golden_dir, "c1")
     ref = [float(l.split("mse")[1]) for l in open(os.path.join(golden_dir, "c1_mse.txt")).read().splitlines()]
@@ -117,12 +182,16 @@ def test_loss_curve_matches_reference_stdout(golden_dir):
     assert it == 100
     assert b1 == pytest.approx(0.9 ** 100, rel=1e-5) and b2 == pytest.approx(0.99 ** 100, rel=1e-5)
     rel = np.abs(mse - np.array(ref[:100])) / np.array(ref[:100])
-    assert "%d itr, mse %.4f" % (0, mse[0]) == "0 itr, mse %.4f" % ref[0]
+    print(f"[{mode}] loss curve: rel[0] {rel[0]:.2e}, max over 50 {rel[:50].max():.2e}, over 100 {rel.max():.2e}")
+    if mode == "exact":
+        assert "%d itr, mse %.4f" % (0, mse[0]) == "0 itr, mse %.4f" % ref[0]
+    else:
+        assert rel[0] <= 2e-6, rel[0]
     assert rel[:50].max() <= 1e-4, rel[:50].max()
     assert rel.max() <= 2e-3, rel.max()
 
 
-def test_single_step_from_identical_state():
+def test_single_step_from_identical_state(mode):
     """One whole iteration (forward, backward, Adam, clamps) from the same uploaded state, incl. Adam moments."""
     rng = np.random.default_rng(3)
     W, H, n = 200, 150, 700
@@ -138,7 +207,7 @@ def test_single_step_from_identical_state():
         mse_gpu = fit.step(1)[0, 0]
         s, a, b1, b2, it = fit.download()
     mse_cpu = st.step(target, p)
-    assert abs(mse_gpu - mse_cpu) <= 1e-7 * mse_cpu
+    assert abs(mse_gpu - mse_cpu) <= (1e-7 if mode == "exact" else 2e-6) * mse_cpu
     assert (b1, b2, it) == (float(st.beta[0]), float(st.beta[1]), st.iteration)
     # Adam turns gradient rounding noise into parameter noise only where |g| is tiny; everywhere else the update
     # agrees to float precision.
@@ -151,11 +220,15 @@ def test_single_step_from_identical_state():
 
 
 @pytest.mark.parametrize("W,H,n,smin,smax", [(97, 61, 300, 1.0, 12.0), (320, 240, 2000, 3.0, 40.0), (64, 64, 50, 100.0, 1024.0)])
-def test_random_states(W, H, n, smin, smax):
-    """Ragged image sizes, splats hanging over the border, wide scale range, random opacity / rotation."""
+def test_random_states(W, H, n, smin, smax, mode):
+    """Ragged image sizes, splats hanging over the border, wide scale range, random opacity / rotation.
+    Rotations are drawn from the arguments for which glibc's sinf / cosf are correctly rounded (safe_rotations), so the
+    device and the oracle work from identical sin / cos and the exact mode must be bit-identical on (nearly) every
+    pixel - the 0.90 this test used to accept was the last-bit sinf / cosf noise of ~2.5 % of the Gaussians spread
+    over the up to 80 Gaussians that cover a pixel here."""
     rng = np.random.default_rng(W * 7 + n)
     target = gs2d.synth_target(W, H, seed=2)
-    splats = random_splats(rng, W, H, n, smin, smax)
+    splats = random_splats(rng, W, H, n, smin, smax, safe_rot=True)
     with gs2d.Fitter(W, H, n) as fit:
         fit.set_target(target)
         fit.upload(splats)
@@ -164,12 +237,25 @@ def test_random_states(W, H, n, smin, smax):
         fit.backward()
         g = fit.grads()
     img_cpu, _, _ = ob.forward(W, H, splats)
-    assert_image_close(img, img_cpu, min_exact=0.90)
+    assert_image_close(img, img_cpu, min_exact=0.999, mode=mode)
     g_cpu = ob.backward(W, H, splats, img_cpu, target)
-    assert_grads_close(g, g_cpu, rtol=5e-4)
+    assert_grads_close(g, g_cpu, rtol=grad_rtol(mode, 5e-4))
 
 
-def test_edge_cases():
+def test_random_states_libm_rotations(exact):
+    """The same with arbitrary rotations: what glibc's last-bit sinf / cosf differences cost in bit-identity."""
+    W, H, n = 320, 240, 2000
+    rng = np.random.default_rng(W * 7 + n)
+    splats = random_splats(rng, W, H, n, 3.0, 40.0)
+    with gs2d.Fitter(W, H, n) as fit:
+        fit.upload(splats)
+        fit.forward()
+        img = fit.image()
+    img_cpu, _, _ = ob.forward(W, H, splats)
+    assert_image_close(img, img_cpu, min_exact=0.90)
+
+
+def test_edge_cases(mode):
     """Empty splat set; splats entirely off-image; degenerate covariance (NaN bounds); exact alpha = 1."""
     W, H = 80, 48
     target = gs2d.synth_target(W, H, seed=9)
@@ -185,7 +271,8 @@ def test_edge_cases():
     s["pos"] = [[-500, -500], [20, 15], [20.5, 15.5], [79.5, 47.5], [40, 24], [1000, 20]]
     s["sx"] = [8, 0, 5, 1024, 3, 8]
     s["sy"] = [8, 0, 5, 1, 3, 8]
-    s["rot"] = [0.3, 0.0, 0.0, 1.0, 0.0, 0.0]
+    s["rot"] = [safe_rotations(np.random.default_rng(1), 1, 0.2, 0.4)[0], 0.0, 0.0,
+                safe_rotations(np.random.default_rng(2), 1, 0.9, 1.1)[0], 0.0, 0.0]
     s["color"] = 0.7
     s["opacity"] = 1.0
     with gs2d.Fitter(W, H, len(s)) as fit:
@@ -196,10 +283,10 @@ def test_edge_cases():
         fit.backward()
         g = fit.grads()
     img_cpu, _, _ = ob.forward(W, H, s)
-    assert_image_close(img, img_cpu, min_exact=0.90)
+    assert_image_close(img, img_cpu, min_exact=0.999, mode=mode)
     g_cpu = ob.backward(W, H, s, img_cpu, target)
     ok = np.isfinite(g_cpu.view(np.float32)).reshape(len(s), 9).all(axis=1)
-    assert_grads_close(g[ok], g_cpu[ok], rtol=1e-3)
+    assert_grads_close(g[ok], g_cpu[ok], rtol=grad_rtol(mode, 1e-3))
 
 
 def test_ellipse_culling_is_a_superset_of_the_footprint():
@@ -380,23 +467,29 @@ def test_independent_images_batch():
         assert np.quantile(np.abs(states[i].view(np.float32) - s1.view(np.float32)), 0.99) <= 1e-3
 
 
-def test_full_size_crop_against_oracle():
-    """BASELINE config 3 size (4096^2, 1 M Gaussians): the oracle cannot afford whole frames in a test, but pixels are
-    independent given the splats, so a 192x160 window rendered by the oracle (splats shifted into window coordinates)
-    must equal the same window of the GPU render up to the rounding of the shifted coordinates."""
-    W = H = 4096
-    n = 1_000_000
-    with gs2d.Fitter(W, H, n) as fit:
-        fit.restart()
-        fit.forward()
-        img = fit.image()
-        st = fit.stats()
-        fit.forward()
-        img2 = fit.image()
-        splats = fit.download(with_adam=False)[0]
-    assert np.array_equal(img, img2)  # idempotent / deterministic
-    assert 10e6 < st["keys"] < 40e6 and 15 * W * H < st["live_pairs"] < 22 * W * H  # SURVEY.md §8d: ~18.5 live / px
-    x0, y0, w, h = 1936, 2064, 192, 160  # multiples of 16 keep x + 0.5 - pos exactly representable after the shift
+def tiled_target_u8(W, H, tile=1024, seed=1):
+    """RGBA8 target of a large image from one synthetic tile repeated (generating 67 M pixels of pcg3d noise on the
+    host would take longer than the test); only the window the oracle looks at has to be known exactly."""
+    t = np.rint(gs2d.synth_target(tile, tile, seed=seed) * 255.0).astype(np.uint8)
+    return np.ascontiguousarray(np.tile(t, ((H + tile - 1) // tile, (W + tile - 1) // tile, 1))[:H, :W])
+
+
+def crop_check(fit, splats, rgba8, window, mode, label):
+    """Forward AND backward of a full-size problem against the oracle on a window. Pixels are independent given the
+    splats, so the oracle renders the window alone (splats shifted into window coordinates; the window origin is a
+    multiple of 16 and the coordinates are below 2^13, so the shift is exact in float), and the gradients of the
+    Gaussians whose whole footprint lies inside the window's interior are complete sums over pixels the oracle has:
+    they must agree like on a small image. What differs: pos.x + u of the footprint solve (main.cpp:508-509) is
+    rounded at a different magnitude after the shift, so a span end that sits within ~1e-3 px of an integer may move by
+    one pixel - a pixel with alpha ~1e-3 at the 3-sigma rim; hence quantiles, not maxima, carry the tight bounds."""
+    x0, y0, w, h = window
+    W, H = fit.W, fit.H
+    fit.forward()
+    img = fit.image()
+    st = fit.stats()
+    fit.backward()
+    g = fit.grads()
+    assert fit.stats()["live_pairs_backward"] == st["live_pairs"]
     s = splats.copy()
     s["pos"][:, 0] -= x0
     s["pos"][:, 1] -= y0
@@ -404,4 +497,103 @@ def test_full_size_crop_against_oracle():
     crop_gpu = img[y0 : y0 + h, x0 : x0 + w]
     # interior only: the crop border clips footprints differently (x < 0 rule, main.cpp:513)
     d = np.abs(crop_gpu[8:-8, 8:-8, :3] - crop_cpu[8:-8, 8:-8, :3])
-    assert np.quantile(d, 0.999) <= 1e-5 and d.max() <= IMG_ATOL, (np.quantile(d, 0.999), d.max())
+    q = np.quantile(d, 0.999)
+    print(f"[{mode}] {label}: crop image q99.9 {q:.3e} max {d.max():.3e}; keys {st['keys']}, live/px {st['live_pairs'] / (W * H):.2f}")
+    assert q <= 1e-5 and d.max() <= IMG_ATOL, (q, d.max())
+    # gradients: Gaussians whose footprint (+ margin) lies inside the interior of the window
+    target_crop = ob.u8_to_target(np.ascontiguousarray(rgba8[y0 : y0 + h, x0 : x0 + w]))
+    g_cpu = ob.backward(w, h, s, crop_cpu, target_crop)
+    r = 3.0 * np.maximum(s["sx"], s["sy"]) + 3.0
+    inside = ((s["pos"][:, 0] - r >= 10) & (s["pos"][:, 0] + r <= w - 10) & (s["pos"][:, 1] - r >= 10) &
+              (s["pos"][:, 1] + r <= h - 10))
+    n_in = int(inside.sum())
+    assert n_in >= 100, n_in
+    rtol = grad_rtol(mode)
+    worst = 0.0
+    for f in ("pos", "sx", "sy", "rot", "color"):
+        a, b = g[f][inside].astype(np.float64), g_cpu[f][inside].astype(np.float64)
+        err = np.abs(a - b) / (np.abs(b) + np.abs(b).mean() + 1e-30)
+        worst = max(worst, err.max())
+        assert np.quantile(err, 0.99) <= rtol, (f, np.quantile(err, 0.99))
+        assert err.max() <= 20 * rtol, (f, err.max())
+    print(f"[{mode}] {label}: gradients of {n_in} Gaussians inside the window, worst rel err {worst:.3e}")
+    return img, g, st
+
+
+def test_full_size_crop_against_oracle(mode):
+    """BASELINE config 3 size (4096^2, 1 M Gaussians): forward and backward against the oracle on a 256x192 window."""
+    W = H = 4096
+    n = 1_000_000
+    rgba8 = tiled_target_u8(W, H)
+    with gs2d.Fitter(W, H, n) as fit:
+        fit.set_target_u8(rgba8)
+        fit.restart()
+        splats = fit.download(with_adam=False)[0]
+        img, g, st = crop_check(fit, splats, rgba8, (1936, 2064, 256, 192), mode, "C3")
+        fit.forward()
+        assert np.array_equal(img, fit.image())  # idempotent / deterministic
+    assert 10e6 < st["keys"] < 40e6 and 15 * W * H < st["live_pairs"] < 22 * W * H  # SURVEY.md §8d: ~18.5 live / px
+
+
+def test_c4_size_crop_and_huge_splats_against_oracle(mode):
+    """BASELINE config 4 size on one GPU (8192^2 = 262 144 tiles, 4 M Gaussians, 128 index slices): forward and
+    backward against the oracle on a window, first with the reference's init(), then with a dozen Gaussians at the
+    1024 scale clamp (main.cpp:744-745) on top - each covers 147 000 tiles, so they go through the overflow path of
+    the slot binning, the in-kernel footprint solve (too tall for the row table) and, with 6 M extra list entries in
+    a few index slices, the 16-bit bucket counters and 32-bit list offsets at their largest."""
+    W = H = 8192
+    n = 4_000_000
+    rgba8 = tiled_target_u8(W, H)
+    window = (4096 + 304, 4096 - 400, 256, 192)
+    with gs2d.Fitter(W, H, n) as fit:
+        fit.set_target_u8(rgba8)
+        fit.restart()
+        splats = fit.download(with_adam=False)[0]
+        _, _, st0 = crop_check(fit, splats, rgba8, window, mode, "C4")
+        assert 40e6 < st0["keys"] < 160e6
+        rng = np.random.default_rng(4)
+        huge = np.concatenate([[0, 1, 2, 3], rng.choice(n, 8, replace=False)])
+        splats["pos"][huge] = rng.uniform(3500, 4700, (len(huge), 2)).astype(np.float32)
+        splats["sx"][huge] = 1024.0
+        splats["sy"][huge] = rng.uniform(700, 1024, len(huge)).astype(np.float32)
+        splats["rot"][huge] = safe_rotations(rng, len(huge))
+        splats["opacity"][huge] = 0.1
+        splats["color"][huge] = rng.uniform(0, 1, (len(huge), 3)).astype(np.float32)
+        fit.upload(splats)
+        _, _, st1 = crop_check(fit, splats, rgba8, window, mode, "C4 + 12 Gaussians at the scale clamp")
+        assert st1["keys"] > st0["keys"] + 1_000_000
+
+
+def test_eight_bands_of_the_headline_config_on_one_gpu():
+    """The 8-rank partition of BASELINE config 3 (tile-row bands, gs2d_set_band) rendered band after band on ONE GPU:
+    images, loss and gradients must add up to the un-sharded result. Keeps the band logic of k_preprocess / the row
+    table / the scan window under test on a 1-GPU box."""
+    W = H = 4096
+    n = 1_000_000
+    rgba8 = tiled_target_u8(W, H)
+    with gs2d.Fitter(W, H, n) as fit:
+        fit.set_target_u8(rgba8)
+        fit.restart()
+        fit.forward()
+        img_full = fit.image()
+        mse_full = fit.last_mse()[0]
+        live_full = fit.stats()["live_pairs"]
+        fit.backward()
+        g_full = fit.grads().view(np.float32).astype(np.float64)
+        img_sum = np.zeros_like(img_full)
+        g_sum = np.zeros_like(g_full)
+        mse_sum, live_sum = 0.0, 0
+        for r in range(8):
+            fit.set_band(r, 8)
+            fit.forward()
+            mse_sum += fit.last_mse()[0]
+            live_sum += fit.stats()["live_pairs"]
+            rows = slice(r * 512, (r + 1) * 512)  # 256 tile rows / 8
+            img_sum[rows] = fit.image()[rows]
+            fit.backward()
+            g_sum += fit.grads().view(np.float32).astype(np.float64)
+    assert np.array_equal(img_sum, img_full)
+    assert live_sum == live_full
+    assert mse_sum == pytest.approx(mse_full, rel=1e-12)
+    scale = np.abs(g_full).mean()
+    assert np.abs(g_sum - g_full).max() <= 2e-4 * (np.abs(g_full).max() + scale)
