@@ -191,10 +191,18 @@ __device__ __forceinline__ double* mailbox_loss( unsigned char* mb, int r, int L
 // Barrier 1: "my backward pass is complete" + all-reduce of the loss. Thread t ships loss[t] to every rank's mailbox,
 // thread r publishes the sequence number to rank r and waits for rank r's; then the partial sums are added in rank
 // order, so every rank computes the identical total.
+// The sequence number of a barrier lives on the device (seq_ctr, one counter per barrier kind, bumped by the kernel
+// itself): every rank runs the identical sequence of barrier kernels, so the counters agree without the host passing
+// them in - which is what lets a multi-rank iteration be replayed as a CUDA graph (no per-launch arguments).
 __global__ void __launch_bounds__( 256 ) k_peer_loss_exchange( Geometry g, PeerPtrs pp, double* __restrict__ loss,
-                                                               unsigned long long seq, DevState* st )
+                                                               unsigned long long* __restrict__ seq_ctr, DevState* st )
 {
 	const int L = g.n_images + 1, me = pp.rank, n = pp.n_ranks;
+	__shared__ unsigned long long seq_s;
+	if( threadIdx.x == 0 )
+		seq_s = ++( *seq_ctr );
+	__syncthreads();
+	const unsigned long long seq = seq_s;
 	for( int t = threadIdx.x; t < L; t += 256 )
 	{
 		const double v = loss[t];
@@ -221,9 +229,14 @@ __global__ void __launch_bounds__( 256 ) k_peer_loss_exchange( Geometry g, PeerP
 }
 
 // Barrier 2: "my stores into your parameter planes are complete" + OR of the non-finite flags.
-__global__ void __launch_bounds__( 32 ) k_peer_barrier2( PeerPtrs pp, unsigned long long seq, DevState* st )
+__global__ void __launch_bounds__( 32 ) k_peer_barrier2( PeerPtrs pp, unsigned long long* __restrict__ seq_ctr,
+                                                         DevState* st )
 {
 	const int me = pp.rank, n = pp.n_ranks, r = threadIdx.x;
+	unsigned long long seq = 0;
+	if( r == 0 )
+		seq = ++( *seq_ctr );
+	seq = __shfl_sync( 0xffffffffu, seq, 0 );
 	int any = 0;
 	if( r < n )
 	{
@@ -477,16 +490,16 @@ int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p,
 #undef PEER_CASE
 	return 1;
 }
-int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long* seq_ctr,
                                cudaStream_t s )
 {
-	k_peer_loss_exchange<<<1, 256, 0, s>>>( g, pp, b.loss, seq, b.state );
+	k_peer_loss_exchange<<<1, 256, 0, s>>>( g, pp, b.loss, seq_ctr, b.state );
 	return 1;
 }
-int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long* seq_ctr,
                           cudaStream_t s )
 {
-	k_peer_barrier2<<<1, 32, 0, s>>>( pp, seq, b.state );
+	k_peer_barrier2<<<1, 32, 0, s>>>( pp, seq_ctr, b.state );
 	return 1;
 }
 int launch_aos_to_soa( const Geometry& g, const Buffers& b, int image, const gs2d_splat* splats_dev,

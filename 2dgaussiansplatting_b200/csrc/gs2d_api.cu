@@ -142,7 +142,7 @@ struct gs2d_ctx
 	{
 		Geometry g;
 		gs2d_params hp;
-		void* ptr[6];
+		void* ptr[8];
 		unsigned long long capacity;
 		int mse_cap, count_live, tune_epoch, pad;
 	};
@@ -179,7 +179,7 @@ struct gs2d_ctx
 	std::vector<void*> ipc_opened;
 	int own_q0 = 0, own_q1 = 0;
 	unsigned char* mbox = nullptr;          // this rank's mailbox (PeerMailbox), mapped by every peer
-	unsigned long long seq1 = 0, seq2 = 0;  // barrier sequence numbers (identical call sequence on every rank)
+	unsigned long long* peer_seq = nullptr; // device: [2] sequence numbers of barrier 1 / barrier 2, bumped by the kernels
 	bool peer_flags = true;                 // barriers over the mailboxes (else tiny NCCL all-reduces): GS2D_PEER_FLAGS
 	// developer timing of the pieces of the peer-memory update (GS2D_PEER_DEBUG=1): events around barrier 1, the
 	// fused kernel, barrier 2 and the gradient clear of every iteration; averages are printed by gs2d_destroy
@@ -374,7 +374,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	                 b.rowrec,     b.rowtab,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots };
+	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -931,7 +931,7 @@ static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_r
 		if( !grads_already_reduced ) // else gs2d_backward has reduced gradients and loss already
 		{
 			if( c->peer_flags )
-				c->launches += launch_peer_loss_exchange( c->g, c->b, c->peers, ++c->seq1, s );
+				c->launches += launch_peer_loss_exchange( c->g, c->b, c->peers, c->peer_seq, s );
 			else
 				e = g_nccl.AllReduce( c->b.loss, c->b.loss, (size_t)c->g.n_images + 1, NCCL_FLOAT64, NCCL_SUM, c->comm, s );
 		}
@@ -946,7 +946,7 @@ static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_r
 		c->launches += launch_adam_peer( c->g, c->b, c->hp, pp, c->own_q0, c->own_q1, s );
 		mark();
 		if( c->peer_flags )
-			c->launches += launch_peer_barrier2( c->g, c->b, c->peers, ++c->seq2, s );
+			c->launches += launch_peer_barrier2( c->g, c->b, c->peers, c->peer_seq + 1, s );
 		else
 			e = g_nccl.AllReduce( &c->b.state->nonfinite, &c->b.state->nonfinite, 1, NCCL_INT32, NCCL_MAX, c->comm, s );
 		if( e )
@@ -1024,7 +1024,11 @@ static int enqueue_iteration( gs2d_ctx* c )
 // n iterations: replays of the captured graph where possible, plain launches otherwise
 static int enqueue_iterations( gs2d_ctx* c, int n )
 {
-	const bool use_graph = n > 0 && !c->profiling && !c->comm && gs2d_tune( "GS2D_GRAPH", 1 ) != 0;
+	// A multi-rank iteration is captured too when its exchange is made of this library's own kernels only (peer-memory
+	// path with flag barriers: their sequence numbers live on the device); the NCCL path keeps plain launches.
+	const bool comm_graph = !c->comm || ( c->peer_update && c->peer_flags && !gs2d_tune( "GS2D_PEER_DEBUG", 0 ) &&
+	                                      gs2d_tune( "GS2D_COMM_GRAPH", 1 ) != 0 );
+	const bool use_graph = n > 0 && !c->profiling && comm_graph && gs2d_tune( "GS2D_GRAPH", 1 ) != 0;
 	if( use_graph )
 	{
 		int rc = apply_pending_target( c ); // stays outside the graph
@@ -1040,6 +1044,8 @@ static int enqueue_iterations( gs2d_ctx* c, int n )
 		key.ptr[3] = c->b.cover;
 		key.ptr[4] = c->b.mse_ring;
 		key.ptr[5] = c->b.bucket_cnt;
+		key.ptr[6] = c->comm;
+		key.ptr[7] = c->peer_update ? (void*)c->peers.mbox[c->rank] : nullptr;
 		key.capacity = c->b.capacity;
 		key.mse_cap = c->b.mse_cap;
 		key.count_live = c->count_live ? 1 : 0;
@@ -1514,6 +1520,8 @@ static int setup_peer_update( gs2d_ctx* c )
 	{
 		CK( cudaMalloc( &c->mbox, peer_mailbox_bytes( c->g.n_images ) ) );
 		CK( cudaMemset( c->mbox, 0, peer_mailbox_bytes( c->g.n_images ) ) );
+		CK( cudaMalloc( &c->peer_seq, 2 * sizeof( unsigned long long ) ) );
+		CK( cudaMemset( c->peer_seq, 0, 2 * sizeof( unsigned long long ) ) );
 	}
 	void* local[5] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v, c->mbox };
 	mine.ok = gs2d_tune( "GS2D_PEER_ADAM", 1 ) ? 1 : 0;

@@ -86,10 +86,10 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 }
 
 // relaxed: write the record in the scaled form the relaxed-arithmetic blend kernels read (SplatRec, gs2d_internal.cuh)
-// rowtab: 1 = splats of at most GS2D_ROWTAB_TILE_ROWS tile rows get their rows solved by k_row_table (else every
+// rowtab: 1 = splats of at most GS2D_ROWTAB_STRIDE rows get their rows solved by k_row_table (else every
 // splat is left to the blend kernels' in-kernel solve: GS2D_ROWTAB=0, the A/B reference)
 template <bool SLOTS>
-__global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const float* __restrict__ params,
+__global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, const float* __restrict__ params,
                                                                SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
                                                                PairOut out, unsigned long long capacity, int cull,
                                                                int relaxed, int rowtab, DevState* __restrict__ st )
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 		const float hmax = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f;
 		const bool off_band = py + hmax < (float)( g.band_ty0 * GS2D_TILE ) || py - hmax > (float)( g.band_ty1 * GS2D_TILE );
 		if( off_band )
-			rowrec[gi].tyr = ROWREC_NONE; // k_row_table looks at every splat
+			rowrec[gi].rows = ROWREC_NONE; // k_row_table looks at every splat
 		else
 		{
 			// cosf/sinf of the reference are glibc's (< 1 ulp, almost always correctly rounded). Evaluate in double and
@@ -166,36 +166,29 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 			r.sinT = s;
 			r.isx3 = xdiv( 1.0f, xmul( xmul( sx, sx ), sx ) );
 			r.isy3 = xdiv( 1.0f, xmul( xmul( sy, sy ), sy ) );
-			// rows of the splat inside the image and inside this rank's band, in tile rows; the row table holds splats
-			// of at most GS2D_ROWTAB_TILE_ROWS tile rows (whole image: the flag must not depend on the band)
+			// rows of the splat inside the image; the row table holds splats of at most GS2D_ROWTAB_STRIDE rows (whole
+			// image: the flag must not depend on the band)
 			const int ry0 = max( begY, 0 ), ry1 = min( endY, g.H - 1 );
-			const bool in_table = rowtab && ry0 <= ry1 && ( ry1 / GS2D_TILE - ry0 / GS2D_TILE ) < GS2D_ROWTAB_TILE_ROWS;
-			r.flags = in_table ? SPLAT_IN_TABLE : 0u;
+			const bool in_table = rowtab && ry0 <= ry1 && ry1 - ry0 < GS2D_ROWTAB_STRIDE;
+			r.flags = in_table ? ( SPLAT_IN_TABLE | ( (unsigned)ry0 << SPLAT_ROW0_SHIFT ) |
+			                       ( (unsigned)( ry1 - ry0 ) << SPLAT_NROWS_SHIFT ) )
+			                   : 0u;
 			float4* dst = reinterpret_cast<float4*>( rec + gi );
-			const float4* src = reinterpret_cast<const float4*>( &r );
-			dst[0] = src[0];
-			dst[1] = src[1];
-			dst[2] = src[2];
-			dst[3] = src[3];
-			RowRec rr;
-			rr.px = px;
-			rr.py = py;
-			rr.a = a;
-			rr.b = b;
-			rr.d = d;
-			rr.begY = begY;
-			rr.endY = endY;
-			rr.tyr = ROWREC_NONE;
+			dst[0] = make_float4( r.px, r.py, r.B, r.D );
+			dst[1] = make_float4( r.A, r.cr, r.cg, r.cb );
+			dst[2] = make_float4( __uint_as_float( r.idx ), __uint_as_float( r.flags ), r.op, r.rotc );
+			dst[3] = make_float4( r.cosT, r.sinT, r.isx3, r.isy3 );
+			// what k_row_table solves: the rows inside the image AND this rank's band
+			unsigned rr_rows = ROWREC_NONE;
 			if( in_table )
 			{
-				const int t0 = max( ry0 / GS2D_TILE, g.band_ty0 ), t1 = min( ry1 / GS2D_TILE, g.band_ty1 - 1 );
-				if( t0 <= t1 )
-					rr.tyr = (unsigned)t0 | ( (unsigned)t1 << 16 );
+				const int b0 = max( ry0, g.band_ty0 * GS2D_TILE ), b1 = min( ry1, g.band_ty1 * GS2D_TILE - 1 );
+				if( b0 <= b1 )
+					rr_rows = (unsigned)b0 | ( (unsigned)( b1 - b0 ) << 20 );
 			}
 			float4* rdst = reinterpret_cast<float4*>( rowrec + gi );
-			const float4* rsrc = reinterpret_cast<const float4*>( &rr );
-			rdst[0] = rsrc[0];
-			rdst[1] = rsrc[1];
+			rdst[0] = make_float4( px, py, a, b );
+			rdst[1] = make_float4( d, __int_as_float( begY ), __int_as_float( endY ), __uint_as_float( rr_rows ) );
 
 			// Conservative tile rectangle. Rows: exactly the reference's [begY, endY]. Columns: every chord of the 3-sigma
 			// ellipse lies within pos.x +- 3*sqrt(cov[0][0]) = 3*sqrt(d*det); widened by 2 px + 1e-4 relative for the
@@ -327,35 +320,48 @@ __global__ void __launch_bounds__( PRE_THREADS ) k_preprocess( Geometry g, const
 
 // ---------------------------------------------------------------------------------------------- row table ---
 // The exact scan-line footprint (solve_quadratic per image row, main.cpp:171-185, :492-509: two IEEE divisions and a
-// square root) used to be solved by the forward blend for every (staged list entry, tile row): 16 rows of every
-// entry of every tile a splat touches, ~4 tiles per tile row, by warps that spend a quarter of their issue slots on
-// it. Here every (splat, image row) is solved ONCE, by a dense grid: one thread per slot of the splat's ring of
-// GS2D_ROWTAB_TILE_ROWS 16-row blocks (a warp = two blocks = 128 contiguous bytes). Slots of tile rows the splat does
-// not reach inside this rank's band are not written (nothing reads them); rows of a reached tile row that lie outside
-// [begY, endY] are written as empty, so the blend needs no row test of its own. Same arithmetic as the in-kernel
-// solve (row_span), so the coverage words - and the image - are bit-identical to it.
+// square root) used to be solved by the forward blend for every (staged list entry, tile row): all 16 rows of every
+// entry of every tile a splat touches (~4 tiles per tile row), by warps that spent a quarter of their issue slots on
+// it. Here every (splat, image row) is solved ONCE, by a dense grid: 8 lanes per splat walk its rows 8 at a time
+// (36..60 rows at the reference's initial scales: 5..8 steps, lanes 82 % busy), 4 splats per warp. Only the rows
+// inside [begY, endY] (and inside the image and this rank's band) are solved and written; the blend masks the other
+// rows of a tile out itself (SplatRec::flags). Same arithmetic as the in-kernel solve (row_span_dense == row_span bit
+// for bit, tests/test_gpu_parity.py::test_row_table_equals_the_in_kernel_solve), so the coverage words - and the
+// image - are identical to it. Measured at 4096^2 / 1 M (profiles/r2_*): 148 M warp-instructions, 0.16 ms at 87 %
+// issue-active, against 0.39 ms of blend time saved.
+// Tried and dropped: the same loop fused into k_preprocess behind (or, for every other warp, in front of) its
+// emission phase, on the reading that the emission leaves 62 % of the issue slots idle - the fused kernel took
+// exactly the sum of the two (0.213 + 0.154 = 0.367 ms at 60 % issue-active, either order): with 10 resident warps
+// per scheduler the solve's dependent chain (sqrt, two divisions) finds no more free slots than it does alone. Two
+// kernels on two streams do not overlap either (the first kernel's blocks hold the SMs).
+#define ROWTAB_LANES 8
 __global__ void __launch_bounds__( 256 ) k_row_table( Geometry g, const RowRec* __restrict__ rowrec,
                                                       unsigned* __restrict__ rowtab )
 {
 	const unsigned t = blockIdx.x * 256u + threadIdx.x;
-	const unsigned gi = t / GS2D_ROWTAB_STRIDE, slot = t % GS2D_ROWTAB_STRIDE;
+	const unsigned gi = t / ROWTAB_LANES, sub = t % ROWTAB_LANES;
 	if( gi >= (unsigned)g.n_total )
 		return;
-	const RowRec* rr = rowrec + gi;
-	const unsigned tyr = rr->tyr;
-	if( tyr == ROWREC_NONE )
+	const float4* rr = reinterpret_cast<const float4*>( rowrec + gi );
+	const float4 q1 = __ldg( rr + 1 ); // d begY endY rows
+	const unsigned rows = (unsigned)__float_as_int( q1.w );
+	if( rows == ROWREC_NONE )
 		return;
-	const int t0 = (int)( tyr & 0xffffu ), t1 = (int)( tyr >> 16 );
-	// the tile row of [t0, t0 + 8) that lives at this ring position
-	const int ty = t0 + ( ( (int)( slot / GS2D_TILE ) - t0 ) & ( GS2D_ROWTAB_TILE_ROWS - 1 ) );
-	if( ty > t1 )
-		return;
-	const float4 q0 = *reinterpret_cast<const float4*>( rr );       // px py a b
-	const float4 q1 = *reinterpret_cast<const float4*>( &rr->d );   // d begY endY tyr
-	const int y = ty * GS2D_TILE + (int)( slot % GS2D_TILE );
-	int begX = 0, endX = 0;
-	const bool any = row_span( q0.x, q0.y, q0.z, q0.w, q1.x, __float_as_int( q1.y ), __float_as_int( q1.z ), y, g.H, begX, endX );
-	rowtab[(size_t)gi * GS2D_ROWTAB_STRIDE + slot] = pack_row_span( any, begX, endX, g.W );
+	const float4 q0 = __ldg( rr );     // px py a b
+	// [y0, y1] lies inside [begY, endY] and inside the image (k_preprocess), so the row tests of row_span are void
+	const int y0 = (int)( rows & 0xfffffu ), y1 = y0 + (int)( rows >> 20 );
+	const float px = q0.x, py = q0.y, a = q0.z, b = q0.w, d = q1.x;
+	const float a4 = xmul( 4.0f, a ), b2 = xmul( 2.0f, b );
+	const bool a_ok = far_from_the_edges( a );
+	const float ra = rcp_refined( a );
+	unsigned* tab = rowtab + (size_t)gi * GS2D_ROWTAB_STRIDE;
+#pragma unroll 1
+	for( int y = y0 + (int)sub; y <= y1; y += ROWTAB_LANES )
+	{
+		int begX = 0, endX = 0;
+		const bool any = row_span_dense( px, py, a, b, d, a4, b2, ra, a_ok, y, begX, endX );
+		tab[y & ( GS2D_ROWTAB_STRIDE - 1 )] = pack_row_span( any, begX, endX, g.W );
+	}
 }
 
 // ------------------------------------------------------------------------------- exclusive scan of the counts ---
@@ -639,7 +645,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	bool forked = false;
 	if( rowtab )
 	{
-		const unsigned rt_blocks = (unsigned)( ( (size_t)g.n_total * GS2D_ROWTAB_STRIDE + 255 ) / 256 );
+		const unsigned rt_blocks = (unsigned)( ( (size_t)g.n_total * ROWTAB_LANES + 255 ) / 256 );
 		cudaStream_t rs = s;
 		if( side && side->stream )
 		{

@@ -176,26 +176,48 @@ __device__ __forceinline__ void gather_record( TileSmem<WSTAGES>& sm, int stage,
 		sm.rec[stage][lane].idx = 0u; // a slot beyond the batch: build_words looks it up like any other (splat 0 exists)
 }
 
-// Exact coverage words of the nb staged entries of `stage`: 16 rows x nb entries. Lane (h = lane >> 4, r = lane & 15)
-// handles row r of entries 2i + h: it fetches the packed span of (splat, image row) from the row table (k_row_table
-// solved it once for all the tiles the row crosses; the 16 rows of an entry are 64 contiguous bytes), clips it to
-// the tile's 16 columns and scatters the mask as two bytes into the block words of the entry. Four entries per lane
-// are in flight at a time.
-// Splats that are not in the row table (taller than GS2D_ROWTAB_TILE_ROWS tile rows, or GS2D_ROWTAB=0) are solved
-// here, in a second loop that a warp enters only if its batch holds one: the reference's quadratic per (entry, tile
-// row) from the unscaled RowRec (row_mask, gs2d_footprint.cuh) - same arithmetic as k_row_table, same words.
+// Exact coverage words of the nb staged entries of `stage`: 16 rows x nb entries.
+// First lane k turns the row range of entry k (SplatRec::flags) into the 16-bit mask of the tile's rows that lie
+// inside it (bit 16: the splat is in the row table) and leaves it in the staged record. Then lane (h = lane >> 4,
+// r = lane & 15) handles row r of entries 2i + h: it fetches the packed span of (splat, image row) from the row table
+// (k_row_table solved it once for all the tiles the row crosses; the 16 rows of an entry are 64 contiguous bytes),
+// clips it to the tile's 16 columns and scatters the mask as two bytes into the block words of the entry. Four
+// entries per lane are in flight at a time.
+// Splats that are not in the row table (taller than GS2D_ROWTAB_STRIDE rows, or GS2D_ROWTAB=0) are solved here, in a
+// second loop that a warp enters only if its batch holds one: the reference's quadratic per (entry, tile row) from
+// the unscaled RowRec (row_mask, gs2d_footprint.cuh) - same arithmetic as k_row_table, same words.
+#define ROWMASK_IN_TABLE 0x10000u
 __device__ __forceinline__ void build_words( TileSmem<1>& sm, int stage, int nb, int lane, int tile_x0, int tile_y,
                                              const unsigned* __restrict__ rowtab, const RowRec* __restrict__ rowrec,
                                              int W, int H )
 {
 	const int h = lane >> 4, r = lane & 15;
-	const unsigned ring = (unsigned)( ( tile_y & ( GS2D_ROWTAB_TILE_ROWS - 1 ) ) * GS2D_TILE + r );
+	const int tile_y0 = tile_y * GS2D_TILE;
+	bool mine_big = false;
+	{
+		// a slot beyond the batch gets "in the table, no row": looked up like any other (gather_record gave it index 0),
+		// masked to nothing
+		unsigned rowmask = ROWMASK_IN_TABLE;
+		if( lane < nb )
+		{
+			const unsigned f = sm.rec[stage][lane].flags;
+			const int ry0 = (int)( ( f >> SPLAT_ROW0_SHIFT ) & ( ( 1u << SPLAT_ROW0_BITS ) - 1u ) );
+			const int nrows = (int)( f >> SPLAT_NROWS_SHIFT ) + 1;
+			const int lo = min( max( ry0 - tile_y0, 0 ), GS2D_TILE ), hi = min( max( ry0 + nrows - tile_y0, 0 ), GS2D_TILE );
+			mine_big = ( f & SPLAT_IN_TABLE ) == 0u;
+			rowmask = mine_big ? 0u : ( ( ( 0xffffffffu << lo ) & ~( 0xffffffffu << hi ) ) | ROWMASK_IN_TABLE );
+		}
+		sm.rec[stage][lane].flags = rowmask;
+	}
+	__syncwarp();
+	const unsigned ring = (unsigned)( ( tile_y0 + r ) & ( GS2D_ROWTAB_STRIDE - 1 ) );
+	const unsigned rbit = 1u << r;
 	// byte (r & 3) of word 2*(r >> 2) of entry h; the right half of the row is 4 bytes on, the next entry pair 64
 	unsigned char* wb0 = reinterpret_cast<unsigned char*>( &sm.words[0][h][0] ) + ( r >> 2 ) * 8 + ( r & 3 );
 	{
-		// every staged slot is processed, valid or not (gather_record gives the slots beyond the batch index 0), and
-		// every entry is looked up, in the table or not (the table is allocated for every splat and was cleared once):
-		// no predicate in the loop; entries that are not in the table are overwritten by the second loop
+		// every staged slot is processed and every entry is looked up, in the table or not (the table is allocated for
+		// every splat and was cleared once): no branch in the loop; what is not in the table, or not a row of the
+		// splat, is masked out (entries that are not in the table are then solved by the second loop)
 		unsigned char* wb = wb0;
 		const SplatRec* s = &sm.rec[stage][h];
 		const unsigned* tab = rowtab + ring;
@@ -203,32 +225,36 @@ __device__ __forceinline__ void build_words( TileSmem<1>& sm, int stage, int nb,
 		for( int k0 = h; k0 < nb; k0 += 8, s += 8, wb += 256 )
 		{
 			unsigned span[4];
-#pragma unroll
-			for( int u = 0; u < 4; u++ )
-				span[u] = __ldg( tab + (size_t)s[2 * u].idx * GS2D_ROWTAB_STRIDE );
+			bool ok[4];
 #pragma unroll
 			for( int u = 0; u < 4; u++ )
 			{
-				const unsigned m = mask_of_span( span[u], tile_x0 );
+				const uint2 f = *reinterpret_cast<const uint2*>( &s[2 * u].idx ); // idx, row mask
+				span[u] = __ldg( tab + (size_t)f.x * GS2D_ROWTAB_STRIDE );
+				ok[u] = ( f.y & rbit ) != 0u;
+			}
+#pragma unroll
+			for( int u = 0; u < 4; u++ )
+			{
+				const unsigned m = ok[u] ? mask_of_span( span[u], tile_x0 ) : 0u;
 				wb[64 * u] = (unsigned char)m;
 				wb[64 * u + 4] = (unsigned char)( m >> 8 );
 			}
 		}
 	}
-	const bool mine_big = lane < nb && ( sm.rec[stage][lane].flags & SPLAT_IN_TABLE ) == 0u;
 	if( __any_sync( 0xffffffffu, mine_big ) )
 	{
-		const int y = tile_y * GS2D_TILE + r;
+		const int y = tile_y0 + r;
 		unsigned char* wb = wb0;
 		const SplatRec* s = &sm.rec[stage][h];
 #pragma unroll 1
 		for( int k = h; k < nb; k += 2, s += 2, wb += 64 )
 		{
-			if( s->flags & SPLAT_IN_TABLE )
+			if( s->flags & ROWMASK_IN_TABLE )
 				continue;
 			const RowRec* rr = rowrec + s->idx;
 			const float4 q0 = __ldg( reinterpret_cast<const float4*>( rr ) );     // px py a b
-			const float4 q1 = __ldg( reinterpret_cast<const float4*>( rr ) + 1 ); // d begY endY tyr
+			const float4 q1 = __ldg( reinterpret_cast<const float4*>( rr ) + 1 ); // d begY endY rows
 			const unsigned m = row_mask( q0.x, q0.y, q0.z, q0.w, q1.x, __float_as_int( q1.y ), __float_as_int( q1.z ), y,
 			                             tile_x0, W, H );
 			wb[0] = (unsigned char)( m & 0xffu );

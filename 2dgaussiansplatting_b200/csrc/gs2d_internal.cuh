@@ -11,6 +11,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "../../include/gs2d.h"
@@ -48,14 +49,19 @@ struct __align__( 16 ) SplatRec
 {
 	float px, py, B, D;        // q0: position; (B, D) and (cg, cb) sit in aligned register pairs (xmul2)
 	float A, cr, cg, cb;       // q1
-	float op;                  // q2: opacity (exact) / opacity^(1/8) (relaxed)
-	unsigned idx;              //     global splat index (row table / RowRec lookup while the coverage words are built)
-	unsigned flags;            //     bit 0: the splat's rows are in the row table (SPLAT_IN_TABLE)
+	unsigned idx;              // q2: global splat index (row table / RowRec lookup while the coverage words are built)
+	unsigned flags;            //     bit 0: the splat's rows are in the row table (SPLAT_IN_TABLE); then bits 1..20 its
+	                           //     first row inside the image, bits 21..27 its number of rows - 1 (<= 127).
+	                           //     (idx, flags) are read as one aligned 64-bit word by build_words
+	float op;                  //     opacity (exact) / opacity^(1/8) (relaxed)
 	float rotc;                //     (sx^2 - sy^2) / (sx^2 sy^2)
 	float cosT, sinT, isx3, isy3; // q3
 };
-static_assert( sizeof( SplatRec ) == 64, "SplatRec must be 64 bytes" );
+static_assert( sizeof( SplatRec ) == 64 && offsetof( SplatRec, idx ) == 32, "SplatRec: 64 bytes, (idx, flags) 8-byte aligned" );
 #define SPLAT_IN_TABLE 1u
+#define SPLAT_ROW0_SHIFT 1
+#define SPLAT_ROW0_BITS 20
+#define SPLAT_NROWS_SHIFT 21
 
 // What the exact scan-line footprint needs (main.cpp:489-509), always unscaled; written by k_preprocess for every
 // splat, read by k_row_table (every splat of the band) and by the blend's in-kernel fallback (splats too tall for the
@@ -65,15 +71,15 @@ struct __align__( 16 ) RowRec
 	float px, py, a, b;
 	float d;
 	int begY, endY;   // row range, main.cpp:490-491 (x86 truncation semantics)
-	unsigned tyr;     // first | last << 16 tile row of the splat inside this rank's band whose rows go into the row
-	                  // table; ROWREC_NONE: no tile, or too tall for the table (more than GS2D_ROWTAB_TILE_ROWS tile rows)
+	unsigned rows;    // first row | number of rows - 1 << 20 of the splat inside the image AND this rank's band: what
+	                  // k_row_table solves; ROWREC_NONE: nothing, or too tall for the table (more than GS2D_ROWTAB_STRIDE rows)
 };
 static_assert( sizeof( RowRec ) == 32, "RowRec must be 32 bytes" );
 #define ROWREC_NONE 0xffffffffu
-// Row table: per splat a ring of GS2D_ROWTAB_TILE_ROWS blocks of 16 packed row spans (pack_row_span), block of tile
-// row ty at ring position ty % GS2D_ROWTAB_TILE_ROWS: 512 bytes per splat, 64 contiguous bytes per (splat, tile row).
-#define GS2D_ROWTAB_TILE_ROWS 8
-#define GS2D_ROWTAB_STRIDE ( GS2D_ROWTAB_TILE_ROWS * GS2D_TILE )
+// Row table: per splat a ring of GS2D_ROWTAB_STRIDE packed row spans (pack_row_span), image row y at ring position
+// y % GS2D_ROWTAB_STRIDE: 512 bytes per splat; the 16 rows of a tile row are 64 contiguous bytes. Only the rows inside
+// [begY, endY] are written; the blend masks the others out with the row range carried in SplatRec::flags.
+#define GS2D_ROWTAB_STRIDE 128
 
 // Loop-carried scalars + flags, one per context, lives in device memory so that gs2d_step can be fully async.
 struct DevState
@@ -219,10 +225,11 @@ static inline size_t peer_mailbox_bytes( int n_images )
 	return sizeof( PeerMailbox ) + sizeof( double ) * GS2D_MAX_RANKS * ( (size_t)n_images + 1 );
 }
 // Barrier 1 + all-reduce of the loss over the mailboxes (replaces ncclAllReduce of n_images + 1 doubles), and
-// barrier 2 + OR of the non-finite flags. One small block each; seq must increase by one per call on every rank.
-int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+// barrier 2 + OR of the non-finite flags. One small block each; seq_ctr: this rank's device-resident counter of the
+// barrier kind, bumped by the kernel (every rank launches the same sequence of barriers).
+int launch_peer_loss_exchange( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long* seq_ctr,
                                cudaStream_t s );
-int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long seq,
+int launch_peer_barrier2( const Geometry& g, const Buffers& b, const PeerPtrs& pp, unsigned long long* seq_ctr,
                           cudaStream_t s );
 int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p, const PeerPtrs& pp, int q0, int q1,
                       cudaStream_t s );

@@ -26,7 +26,12 @@ GRAD_RTOL = 2e-4
 # Relaxed arithmetic (GS2D_EXACT=0, the library's default; gs2d_forward.cu): alpha = ( s (1 - d2/16) )^8 with FMA
 # contraction and s = opacity^(1/8) folded into the inverse covariance: ~3 ulp on the argument, x8 through the power
 # => alpha within ~2e-6 relative; colour = sum of <= ~100 such terms in [0, 1].
-RELAXED_IMG_TOL = 1e-5       # 99.99 % of the pixels; the rest is bounded by one flipped T < 1/256 decision (IMG_ATOL)
+# Measured on a B200 (gpurun_out/r2a_pytest.log): image q99.99 <= 4.5e-7 on every configuration but the edge cases,
+# where a 1024 x 1 needle (d2 = a difference of terms of size 1e3) reaches 2e-5; gradients <= 3e-5 relative on the
+# reference's configurations, 8e-4 on 50 Gaussians of 100..1024 px; loss curve of the 268 x 213 fit 7e-10 at iteration
+# 0, 1.1e-6 over 50 iterations (exact mode: 6.5e-7).
+RELAXED_IMG_TOL = 2e-6       # 99.99 % of the pixels; the rest is bounded by one flipped T < 1/256 decision (IMG_ATOL)
+RELAXED_IMG_TOL_NEEDLES = 1e-4  # ill-conditioned Gaussians (aspect ratio ~1000)
 RELAXED_GRAD_RTOL = 1e-3     # |dg| <= rtol * (|g| + mean|g|)
 MODES = ["exact", "relaxed"]
 
@@ -96,7 +101,7 @@ def random_splats(rng, W, H, n, smin=2.0, smax=24.0, opacity=(0.1, 1.0), safe_ro
     return s
 
 
-def assert_image_close(img_gpu, img_cpu, min_exact=0.98, mode="exact"):
+def assert_image_close(img_gpu, img_cpu, min_exact=0.98, mode="exact", relaxed_tol=RELAXED_IMG_TOL):
     """exact mode: >= min_exact of the pixels bit-identical, >= 99.99 % within 4 ulp of 1.0 (a last-bit difference of
     cosf/sinf on one of the covering splats), and nothing beyond one flipped coverage / liveness decision (IMG_ATOL).
     relaxed mode: >= 99.99 % within RELAXED_IMG_TOL, nothing beyond IMG_ATOL."""
@@ -110,7 +115,7 @@ def assert_image_close(img_gpu, img_cpu, min_exact=0.98, mode="exact"):
         assert same.mean() >= min_exact, f"only {same.mean():.5f} of the pixels are bit-identical (max diff {d})"
         assert (diff <= 5e-7).mean() >= 0.9999, (diff <= 5e-7).mean()
     else:
-        assert (diff <= RELAXED_IMG_TOL).mean() >= 0.9999, ((diff <= RELAXED_IMG_TOL).mean(), np.quantile(diff, 0.9999))
+        assert (diff <= relaxed_tol).mean() >= 0.9999, ((diff <= relaxed_tol).mean(), np.quantile(diff, 0.9999))
     assert d <= IMG_ATOL, d
     return same.mean(), d
 
@@ -239,7 +244,7 @@ def test_random_states(W, H, n, smin, smax, mode):
     img_cpu, _, _ = ob.forward(W, H, splats)
     assert_image_close(img, img_cpu, min_exact=0.999, mode=mode)
     g_cpu = ob.backward(W, H, splats, img_cpu, target)
-    assert_grads_close(g, g_cpu, rtol=grad_rtol(mode, 5e-4))
+    assert_grads_close(g, g_cpu, rtol=grad_rtol(mode, 5e-4) * (3 if smax > 100 else 1))
 
 
 def test_random_states_libm_rotations(exact):
@@ -283,7 +288,7 @@ def test_edge_cases(mode):
         fit.backward()
         g = fit.grads()
     img_cpu, _, _ = ob.forward(W, H, s)
-    assert_image_close(img, img_cpu, min_exact=0.999, mode=mode)
+    assert_image_close(img, img_cpu, min_exact=0.999, mode=mode, relaxed_tol=RELAXED_IMG_TOL_NEEDLES)
     g_cpu = ob.backward(W, H, s, img_cpu, target)
     ok = np.isfinite(g_cpu.view(np.float32)).reshape(len(s), 9).all(axis=1)
     assert_grads_close(g[ok], g_cpu[ok], rtol=grad_rtol(mode, 1e-3))
@@ -338,6 +343,37 @@ def test_slot_binning_equals_the_triple_path():
         (img0, st0), (img1, st1) = out
         assert img0.tobytes() == img1.tobytes()
         assert st0["live_pairs"] == st1["live_pairs"] and st0["keys"] == st1["keys"]
+
+
+def test_row_table_equals_the_in_kernel_solve():
+    """k_row_table solves every (Gaussian, image row) once with hand-scheduled IEEE division / square root sequences
+    (row_span_dense); the blend's own in-kernel solve (row_mask, the path of Gaussians taller than 128 rows and of
+    GS2D_ROWTAB=0) uses div.rn / sqrt.rn. Both must give the same coverage words: bit-identical images, same live
+    pairs - round Gaussians, needles at every angle, tiny ones, ones hanging over the border, mixed with tall ones."""
+    W, H = 700, 520
+    rng = np.random.default_rng(31)
+    cases = [random_splats(rng, W, H, 6000, smin=2, smax=14), random_splats(rng, W, H, 3000, smin=1, smax=40),
+             random_splats(rng, W, H, 800, smin=1, smax=60)]
+    cases[1]["sy"][:] = rng.uniform(1, 2.5, 3000)  # needles
+    cases[2]["sx"][::7] = rng.uniform(100, 900, len(cases[2]["sx"][::7]))  # some far too tall for the table
+    for splats in cases:
+        out = []
+        for rowtab in (0, 1):
+            gs2d.set_tuning("GS2D_ROWTAB", rowtab)
+            try:
+                with gs2d.Fitter(W, H, len(splats)) as fit:
+                    fit.set_target(gs2d.synth_target(W, H, seed=3))
+                    fit.upload(splats)
+                    fit.forward()
+                    img, st = fit.image(), fit.stats()
+                    mse = fit.step(3)[:, 0]
+                    out.append((img, st, mse))
+            finally:
+                gs2d.set_tuning("GS2D_ROWTAB", 1)
+        (img0, st0, mse0), (img1, st1, mse1) = out
+        assert img0.tobytes() == img1.tobytes()
+        assert st0["live_pairs"] == st1["live_pairs"] and st0["keys"] == st1["keys"]
+        assert mse0[0] == mse1[0] and np.allclose(mse0, mse1, rtol=1e-6)
 
 
 def test_binning_switches_paths_when_slot_rows_overflow():
