@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "gs2d_comm_init", "gs2d_set_band", "gs2d_last_step_ms", "gs2d_profile_step", "gs2d_launch_count", "gs2d_sync",
     "gs2d_set_profiling", "gs2d_get_profile", "gs2d_set_stats", "gs2d_set_tuning",
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
-    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_comm_mode", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
+    "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_comm_mode", "gs2d_comm_traffic", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
     "gs2d_image_load_rgba8", "gs2d_image_decode_jpeg_rgba8", "gs2d_image_free", "gs2d_image_write_ppm",
     "gs2d_overlay_geometry",
 ]
@@ -116,6 +116,7 @@ def load_library():
     L.gs2d_comm_init.argtypes = [vp, i, i, vp]
     L.gs2d_set_band.argtypes = [vp, i, i]
     L.gs2d_comm_mode.argtypes = [vp, C.POINTER(i), C.POINTER(i)]
+    L.gs2d_comm_traffic.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(i), i]
     L.gs2d_last_step_ms.argtypes = [vp, C.POINTER(f)]
     L.gs2d_profile_step.argtypes = [vp, C.POINTER(f * 6)]
     L.gs2d_set_profiling.argtypes = [vp, i]
@@ -397,6 +398,16 @@ class Fitter:
         n, p = C.c_int(), C.c_int()
         self._ck(self.lib.gs2d_comm_mode(self._ctx, C.byref(n), C.byref(p)))
         return n.value, bool(p.value)
+
+
+def _comm_traffic(self, reset=False):
+    """-> (bytes read from peers, bytes written to peers, sparse): NVLink payload of the peer-memory exchange."""
+    r, w, s = C.c_uint64(), C.c_uint64(), C.c_int()
+    self._ck(self.lib.gs2d_comm_traffic(self._ctx, C.byref(r), C.byref(w), C.byref(s), int(bool(reset))))
+    return r.value, w.value, bool(s.value)
+
+
+Fitter.comm_traffic = _comm_traffic
 
 
 def _take_image(rc, p, w, h):

@@ -259,6 +259,29 @@ __global__ void __launch_bounds__( 32 ) k_peer_barrier2( PeerPtrs pp, unsigned l
 // the peer pointers live in registers and all NR loads are issued before the first add). Gradients are summed in
 // rank order (deterministic), and every splat is updated by exactly one rank, so the replicated parameters stay
 // bit-identical on all ranks.
+__device__ __forceinline__ unsigned ld_sys_u32( const unsigned* p )
+{
+	unsigned v;
+	asm volatile( "ld.volatile.global.u32 %0, [%1];" : "=r"( v ) : "l"( p ) );
+	return v;
+}
+// bit r: a Gaussian with centre row py and scales sx, sy can reach the band of rank r (tile rows [r * per, (r+1) * per)).
+// The receiver's own test (k_preprocess: py +- (3 max(|sx|, |sy|) * 1.001 + 2)) is applied to the parameters AFTER this
+// iteration's Adam step, this one to those before it: one step moves py and the scales by lr each (the first Adam step
+// of a parameter is +-lr, later ones smaller), so 1 px more on each side makes it a superset. NaN reaches everyone,
+// like there.
+__device__ __forceinline__ unsigned reach_mask( float py, float sx, float sy, int per_rows_px, int n_ranks, float slack )
+{
+	const float h = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f + slack;
+	unsigned m = 0;
+	for( int r = 0; r < n_ranks; r++ )
+	{
+		const bool off = py + h < (float)( r * per_rows_px ) || py - h > (float)( ( r + 1 ) * per_rows_px );
+		m |= off ? 0u : ( 1u << r );
+	}
+	return m;
+}
+
 template <int NR>
 __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, float* __restrict__ adam_m,
                                                       float* __restrict__ adam_v, gs2d_params hp,
@@ -273,6 +296,19 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	const int pl = blockIdx.y;
 	const size_t o = (size_t)pl * g.n_pad + i4;
 	const bool optimised = pl != PL_OP || hp.optimize_opacity;
+	// which ranks may hold a non-zero gradient for this quad (their band test passed one of its Gaussians)
+	unsigned tmask = ( 1u << NR ) - 1u;
+	if( pp.sparse && pp.sum_all )
+	{
+		unsigned w[NR];
+#pragma unroll
+		for( int r = 0; r < NR; r++ )
+			w[r] = ld_sys_u32( pp.touch[r] + ( q >> 5 ) ); // one word per 32 consecutive quads: a broadcast per warp
+		tmask = 0;
+#pragma unroll
+		for( int r = 0; r < NR; r++ )
+			tmask |= ( ( w[r] >> ( q & 31 ) ) & 1u ) << r;
+	}
 	float gv[4] = { 0.f, 0.f, 0.f, 0.f };
 	if( optimised )
 	{
@@ -281,7 +317,7 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 			float4 part[NR];
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
-				part[r] = ld_sys4( pp.grads[r] + o ); // NR loads in flight
+				part[r] = ( ( tmask >> r ) & 1u ) ? ld_sys4( pp.grads[r] + o ) : make_float4( 0.f, 0.f, 0.f, 0.f ); // in flight together
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
 			{
@@ -334,11 +370,47 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	const float4 out = make_float4( pv[0], pv[1], pv[2], pv[3] );
 	// a parameter that cannot have changed (opacity while it is not optimised and already inside its clamp) is not sent
 	const bool changed = optimised || out.x != p.x || out.y != p.y || out.z != p.z || out.w != p.w;
+	// whom to send it to: everyone (dense), or the ranks a Gaussian of the quad reaches now or reached last time
+	unsigned send = ( 1u << NR ) - 1u;
+	if( pp.sparse )
+	{
+		const float* own = pp.params[pp.rank];
+		const float4 py = *reinterpret_cast<const float4*>( own + (size_t)PL_PY * g.n_pad + i4 );
+		const float4 sx = *reinterpret_cast<const float4*>( own + (size_t)PL_SX * g.n_pad + i4 );
+		const float4 sy = *reinterpret_cast<const float4*>( own + (size_t)PL_SY * g.n_pad + i4 );
+		// these may be the values before or after this very kernel's update of the three planes (their threads run
+		// concurrently): the slack covers one Adam step either way
+		const int per_px = pp.band_tile_rows * GS2D_TILE;
+		const float slack = 1.0f + 3.0f * hp.lr * 1.001f + hp.lr;
+		const unsigned now = reach_mask( py.x, sx.x, sy.x, per_px, NR, slack ) | reach_mask( py.y, sx.y, sy.y, per_px, NR, slack ) |
+		                     reach_mask( py.z, sx.z, sy.z, per_px, NR, slack ) | reach_mask( py.w, sx.w, sy.w, per_px, NR, slack );
+		const int par = st->iteration & 1; // k_advance has run: the parity of the iteration being finished
+		const size_t nq = (size_t)g.n_pad / 4;
+		const unsigned prev = pp.reach_prev[(size_t)par * nq + q];
+		send = now | prev | ( 1u << pp.rank );
+		if( pl == 0 )
+			pp.reach_prev[(size_t)( par ^ 1 ) * nq + q] = (unsigned char)now;
+	}
 	if( changed )
 	{
 #pragma unroll
 		for( int r = 0; r < NR; r++ )
-			*reinterpret_cast<float4*>( pp.params[r] + o ) = out;
+			if( ( send >> r ) & 1u )
+				*reinterpret_cast<float4*>( pp.params[r] + o ) = out;
+	}
+	if( pp.traffic )
+	{
+		// NVLink quads of this warp: gradient quads read from peers, parameter quads written to peers
+		const unsigned peers = ( ( 1u << NR ) - 1u ) & ~( 1u << pp.rank );
+		unsigned nr = ( optimised && pp.sum_all ) ? __popc( tmask & peers ) : 0u, nw = changed ? __popc( send & peers ) : 0u;
+		const unsigned act = __activemask(); // the last warp of the slice may be partial
+		nr = __reduce_add_sync( act, nr );
+		nw = __reduce_add_sync( act, nw );
+		if( ( threadIdx.x & 31 ) == __ffs( act ) - 1 )
+		{
+			atomicAdd( pp.traffic, (unsigned long long)nr );
+			atomicAdd( pp.traffic + 1, (unsigned long long)nw );
+		}
 	}
 	if( bad )
 		atomicOr( &st->nonfinite, 1 );

@@ -180,6 +180,10 @@ struct gs2d_ctx
 	int own_q0 = 0, own_q1 = 0;
 	unsigned char* mbox = nullptr;          // this rank's mailbox (PeerMailbox), mapped by every peer
 	unsigned long long* peer_seq = nullptr; // device: [2] sequence numbers of barrier 1 / barrier 2, bumped by the kernels
+	unsigned* touch_mem = nullptr;          // device: this rank's touch bitmap (Buffers::touch points here while the sparse exchange is on)
+	unsigned char* reach_prev = nullptr;    // device: PeerPtrs::reach_prev
+	unsigned long long* peer_traffic = nullptr; // device: PeerPtrs::traffic
+	long long traffic_iter0 = 0;            // expected_iteration when the traffic counters were last reset
 	bool peer_flags = true;                 // barriers over the mailboxes (else tiny NCCL all-reduces): GS2D_PEER_FLAGS
 	// developer timing of the pieces of the peer-memory update (GS2D_PEER_DEBUG=1): events around barrier 1, the
 	// fused kernel, barrier 2 and the gradient clear of every iteration; averages are printed by gs2d_destroy
@@ -374,7 +378,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	                 b.rowrec,     b.rowtab,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq };
+	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->peer_traffic };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -694,6 +698,9 @@ static int write_state( gs2d_ctx* c, float b1t, float b2t, int iteration )
 	s.iteration = iteration;
 	*c->h_state = s;
 	CK( cudaMemcpyAsync( c->b.state, c->h_state, sizeof( DevState ), cudaMemcpyHostToDevice, c->stream ) );
+	// every rank holds the complete new state: the next exchange sends every quad to everyone once (sparse exchange)
+	if( c->reach_prev )
+		CK( cudaMemsetAsync( c->reach_prev, 0xff, 2 * ( (size_t)c->g.n_pad / 4 ), c->stream ) );
 	CK( cudaStreamSynchronize( c->stream ) );
 	c->expected_iteration = iteration;
 	c->have_forward = false;
@@ -811,10 +818,12 @@ extern "C" int gs2d_download_state( gs2d_ctx* c, int image, gs2d_splat* splats, 
 	int rc = resolve( c );
 	if( rc && rc != GS2D_ERR_NONFINITE )
 		return rc;
-	if( adam && c->comm && c->peer_update )
+	if( ( adam || splats ) && c->comm && c->peer_update )
 	{
-		// the Adam moments of a slice live on the rank that owns it: fetch the other slices over NVLink. The peers are
-		// quiescent: they cannot start their next update before this rank joins the next iteration's all-reduce.
+		// the Adam moments of a slice live on the rank that owns it, and with the sparse exchange so does the only
+		// complete copy of its parameters (this rank's copy is exact for the Gaussians that reach its band, stale for
+		// the others): fetch the other slices over NVLink. The peers are quiescent: they cannot start their next update
+		// before this rank joins the next iteration's barrier.
 		for( int r = 0; r < c->n_ranks; r++ )
 		{
 			int q0, q1;
@@ -824,8 +833,13 @@ extern "C" int gs2d_download_state( gs2d_ctx* c, int image, gs2d_splat* splats, 
 			for( int pl = 0; pl < GS2D_NPLANES; pl++ )
 			{
 				const size_t o = (size_t)pl * c->g.n_pad + (size_t)q0 * 4, bytes = sizeof( float ) * 4 * (size_t)( q1 - q0 );
-				CK( cudaMemcpyAsync( c->b.adam_m + o, c->peer_m[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
-				CK( cudaMemcpyAsync( c->b.adam_v + o, c->peer_v[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
+				if( adam )
+				{
+					CK( cudaMemcpyAsync( c->b.adam_m + o, c->peer_m[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
+					CK( cudaMemcpyAsync( c->b.adam_v + o, c->peer_v[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
+				}
+				if( splats && c->peers.sparse && !gs2d_tune( "GS2D_DOWNLOAD_LOCAL", 0 ) ) // (developer knob: this rank's own copy)
+					CK( cudaMemcpyAsync( c->b.params + o, c->peers.params[r] + o, bytes, cudaMemcpyDeviceToDevice, c->stream ) );
 			}
 		}
 	}
@@ -1509,9 +1523,10 @@ static int setup_peer_update( gs2d_ctx* c )
 	if( n > GS2D_MAX_RANKS || !g_nccl.AllGather )
 		return GS2D_OK;
 	cudaStream_t s = c->stream;
+	const int NH = 6;
 	struct Blob
 	{
-		cudaIpcMemHandle_t h[5];
+		cudaIpcMemHandle_t h[6];
 		int ok;
 		int pad[3];
 	};
@@ -1522,11 +1537,18 @@ static int setup_peer_update( gs2d_ctx* c )
 		CK( cudaMemset( c->mbox, 0, peer_mailbox_bytes( c->g.n_images ) ) );
 		CK( cudaMalloc( &c->peer_seq, 2 * sizeof( unsigned long long ) ) );
 		CK( cudaMemset( c->peer_seq, 0, 2 * sizeof( unsigned long long ) ) );
+		const size_t touch_bytes = sizeof( unsigned ) * ( (size_t)c->g.n_pad / 128 + 1 ), nq = (size_t)c->g.n_pad / 4;
+		CK( cudaMalloc( &c->touch_mem, touch_bytes ) );
+		CK( cudaMemset( c->touch_mem, 0, touch_bytes ) );
+		CK( cudaMalloc( &c->reach_prev, 2 * nq ) );
+		CK( cudaMemset( c->reach_prev, 0xff, 2 * nq ) );
+		CK( cudaMalloc( &c->peer_traffic, 2 * sizeof( unsigned long long ) ) );
+		CK( cudaMemset( c->peer_traffic, 0, 2 * sizeof( unsigned long long ) ) );
 	}
-	void* local[5] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v, c->mbox };
+	void* local[6] = { c->b.grads, c->b.params, c->b.adam_m, c->b.adam_v, c->mbox, c->touch_mem };
 	mine.ok = gs2d_tune( "GS2D_PEER_ADAM", 1 ) ? 1 : 0;
 	c->peer_flags = gs2d_tune( "GS2D_PEER_FLAGS", 1 ) != 0;
-	for( int k = 0; k < 5 && mine.ok; k++ )
+	for( int k = 0; k < NH && mine.ok; k++ )
 		if( cudaIpcGetMemHandle( &mine.h[k], local[k] ) != cudaSuccess )
 			mine.ok = 0;
 	cudaGetLastError();
@@ -1549,9 +1571,9 @@ static int setup_peer_update( gs2d_ctx* c )
 	pp.sum_all = 1;
 	for( int r = 0; r < n && ok; r++ )
 	{
-		void* ptr[5] = { local[0], local[1], local[2], local[3], local[4] };
+		void* ptr[6] = { local[0], local[1], local[2], local[3], local[4], local[5] };
 		if( r != c->rank )
-			for( int k = 0; k < 5 && ok; k++ )
+			for( int k = 0; k < NH && ok; k++ )
 			{
 				if( cudaIpcOpenMemHandle( &ptr[k], all[r].h[k], cudaIpcMemLazyEnablePeerAccess ) != cudaSuccess )
 				{
@@ -1566,7 +1588,12 @@ static int setup_peer_update( gs2d_ctx* c )
 		c->peer_m[r] = (float*)ptr[2];
 		c->peer_v[r] = (float*)ptr[3];
 		pp.mbox[r] = (unsigned char*)ptr[4];
+		pp.touch[r] = (const unsigned*)ptr[5];
 	}
+	pp.sparse = gs2d_tune( "GS2D_PEER_SPARSE", 1 ) ? 1 : 0;
+	pp.reach_prev = c->reach_prev;
+	pp.traffic = c->peer_traffic;
+	pp.band_tile_rows = ( c->g.tiles_y + n - 1 ) / n; // set_band
 	// agree: the peer path is used only if every rank mapped every peer
 	int* flag = reinterpret_cast<int*>( dev );
 	CK( cudaMemcpyAsync( flag, &ok, sizeof( int ), cudaMemcpyHostToDevice, s ) );
@@ -1580,6 +1607,7 @@ static int setup_peer_update( gs2d_ctx* c )
 	cudaFree( dev );
 	if( e )
 		return nccl_fail( c, "peer setup collective", e );
+	c->b.touch = ( agreed && pp.sparse ) ? c->touch_mem : nullptr; // dense exchange or NCCL path: k_preprocess sets no bits
 	if( agreed )
 	{
 		c->peers = pp;
@@ -1603,6 +1631,28 @@ extern "C" int gs2d_comm_mode( const gs2d_ctx* c, int* n_ranks, int* peer_memory
 		*n_ranks = c->comm ? c->n_ranks : 1;
 	if( peer_memory )
 		*peer_memory = ( c->comm && c->peer_update ) ? 1 : 0;
+	return GS2D_OK;
+}
+
+extern "C" int gs2d_comm_traffic( gs2d_ctx* c, uint64_t* bytes_read, uint64_t* bytes_written, int* sparse, int reset )
+{
+	if( !c )
+		return GS2D_ERR_INVALID;
+	unsigned long long t[2] = { 0, 0 };
+	if( c->comm && c->peer_update && c->peer_traffic )
+	{
+		CK( cudaSetDevice( c->device ) );
+		CK( cudaStreamSynchronize( c->stream ) );
+		CK( cudaMemcpy( t, c->peer_traffic, sizeof( t ), cudaMemcpyDeviceToHost ) );
+		if( reset )
+			CK( cudaMemset( c->peer_traffic, 0, sizeof( t ) ) );
+	}
+	if( bytes_read )
+		*bytes_read = 16ull * t[0];
+	if( bytes_written )
+		*bytes_written = 16ull * t[1];
+	if( sparse )
+		*sparse = ( c->comm && c->peer_update && c->peers.sparse ) ? 1 : 0;
 	return GS2D_OK;
 }
 

@@ -92,7 +92,8 @@ template <bool SLOTS>
 __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, const float* __restrict__ params,
                                                                SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
                                                                PairOut out, unsigned long long capacity, int cull,
-                                                               int relaxed, int rowtab, DevState* __restrict__ st )
+                                                               int relaxed, int rowtab, unsigned* __restrict__ touch,
+                                                               DevState* __restrict__ st )
 {
 	const int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 	sb.local = 0;
 	sb.k.begY = 1;
 	sb.k.endY = 0;
+	bool in_band = false; // passed the band test: the only splats that can receive a gradient on this rank
 	if( gi < g.n_total )
 	{
 		const float px = params[PL_PX * g.n_pad + gi];
@@ -120,6 +122,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 		// 2 px and 1e-3 relative cover the truncation and the float error of the exact bound. NaNs fall through.
 		const float hmax = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f;
 		const bool off_band = py + hmax < (float)( g.band_ty0 * GS2D_TILE ) || py - hmax > (float)( g.band_ty1 * GS2D_TILE );
+		in_band = !off_band;
 		if( off_band )
 			rowrec[gi].rows = ROWREC_NONE; // k_row_table looks at every splat
 		else
@@ -225,6 +228,21 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 			sb.k.delta = span_delta( px, hx, cull );
 			sb.k.begY = begY;
 			sb.k.endY = endY;
+		}
+	}
+	if( touch )
+	{
+		// sparse gradient exchange (PeerPtrs::touch): one bit per quad of 4 consecutive splats, the 8 quads of a warp
+		// are 8 aligned bits of one word
+		const unsigned bal = __ballot_sync( 0xffffffffu, in_band );
+		if( lane == 0 && bal )
+		{
+			unsigned bits = 0;
+#pragma unroll
+			for( int qd = 0; qd < 8; qd++ )
+				bits |= ( ( bal >> ( 4 * qd ) ) & 0xfu ) ? ( 1u << qd ) : 0u;
+			const unsigned q = (unsigned)gi >> 2; // first quad of the warp: a multiple of 8
+			atomicOr( touch + ( q >> 5 ), bits << ( q & 31u ) );
 		}
 	}
 	const bool has = sb.ty0 <= sb.ty1 && sb.rtx0 <= sb.rtx1;
@@ -622,6 +640,8 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	}
 	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
 	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ), s );
+	if( b.touch )
+		cudaMemsetAsync( b.touch, 0, sizeof( unsigned ) * ( (size_t)g.n_pad / 128 + 1 ), s );
 	const bool slots = use_slots && gs2d_tune( "GS2D_SLOTS", 1 ) != 0;
 	PairOut po;
 	po.triple = b.triples;
@@ -633,10 +653,10 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
 	if( slots )
 		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                               relaxed, rowtab, b.state );
+		                                               relaxed, rowtab, b.touch, b.state );
 	else
 		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                                relaxed, rowtab, b.state );
+		                                                relaxed, rowtab, b.touch, b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );

@@ -157,6 +157,7 @@ struct Buffers
 	float4* image;            // [n_images][H][W]
 	double* loss_partial;     // [n_tiles_total]
 	unsigned* tile_done;      // [n_tiles_total] forward -> backward tile flags of the PDL overlap (gs2d_blend.cuh)
+	unsigned* touch;          // [n_pad / 128 + 1] bitmap of the quads that passed this rank's band test (PeerPtrs::touch); nullptr on one GPU
 	unsigned long long* live_slots;   // [GS2D_LIVE_SLOTS]
 	unsigned long long* staged_slots; // [GS2D_LIVE_SLOTS], contiguous after live_slots
 	unsigned long long* stats;        // [2] live pairs, staged entries of the last forward (summed slots)
@@ -206,6 +207,21 @@ struct PeerPtrs
 	float* params[GS2D_MAX_RANKS];
 	int n_ranks, rank;
 	int sum_all; // 1: sum the gradients of all ranks; 0: this rank's gradients are already the total
+	// Sparse exchange (GS2D_PEER_SPARSE, default on). A Gaussian reaches 1.15 of 8 bands on average, so most of what the
+	// dense exchange moves is zeros (gradients) or parameters the receiver never looks at:
+	//   touch[r] : rank r's bitmap of the quads (4 consecutive Gaussians) that passed its band test in k_preprocess this
+	//              iteration, i.e. that CAN hold a non-zero gradient on r; the owner of a quad reads the gradient quads
+	//              of the ranks whose bit is set and takes zeros for the others;
+	//   reach    : the owner sends a quad's new parameters only to the ranks whose band a Gaussian of the quad can
+	//              reach (rows py +- (3 max(sx, sy) + margin), a superset of the receiver's own band test after one
+	//              Adam step) - and once more to a rank it has just stopped reaching, so that the receiver's stale copy
+	//              is one its band test rejects. A rank's copy of the parameters is therefore exact for every Gaussian
+	//              its kernels look at; gs2d_download_state gathers the rest from the owners.
+	const unsigned* touch[GS2D_MAX_RANKS];
+	unsigned char* reach_prev; // [2][n_pad / 4] double-buffered by iteration parity: ranks reached at the last exchange
+	unsigned long long* traffic; // [2] 16-byte quads read from / written to peers over NVLink (running sums)
+	int sparse;
+	int band_tile_rows;        // tile rows per rank (set_band)
 	// mailboxes for the flag barriers (one per rank, mapped everywhere): see PeerMailbox
 	unsigned char* mbox[GS2D_MAX_RANKS];
 };

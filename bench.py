@@ -299,6 +299,8 @@ def run_ours(args):
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
+    if comm_mode is not None:
+        fit.comm_traffic(reset=True)
     fit.step(1, want_mse=False)
     launches0 = fit.launch_count()
     t0 = time.perf_counter()
@@ -308,6 +310,10 @@ def run_ours(args):
     dev_ms = fit.last_step_ms()  # CUDA events on the library's stream around exactly the K iterations
     clocks = sampler.stop()
     launches = fit.launch_count() - launches0
+    nvlink = None
+    if comm_mode is not None:
+        rd, wr, sparse = fit.comm_traffic()
+        nvlink = [rd / (K + 1), wr / (K + 1), 1.0 if sparse else 0.0]  # the aligning iteration is counted too
     barrier()
 
     # ---- per-kernel-group times (untimed for `value`): the same iterations with CUDA events between the groups ----
@@ -332,6 +338,20 @@ def run_ours(args):
         dist.all_reduce(live, op=dist.ReduceOp.SUM)
         live[2] /= world
     dev_ms, wall_ms, exact_ms = float(t[0]), float(t[1]), float(t[2])
+    exchange = None
+    if nvlink is not None:
+        tv = torch.tensor(nvlink, dtype=torch.float64, device="cuda")
+        dist.all_reduce(tv, op=dist.ReduceOp.SUM)
+        plane_mb = 9 * 4 * (N + 7) / 1e6
+        exchange = {
+            "path": "peer_memory" if comm_mode[1] else "nccl_allreduce", "sparse": bool(tv[2] > 0),
+            "nvlink_mb_per_step_per_rank": {"gradients_read": float(tv[0]) / world / 1e6,
+                                            "parameters_written": float(tv[1]) / world / 1e6},
+            "dense_equivalent_mb_per_step_per_rank": {"gradients_read": plane_mb * (world - 1) / world,
+                                                      "parameters_written": plane_mb * (world - 1) / world},
+            "what": "payload counted by the exchange kernel itself (16-byte quads), mean over the timed iterations; "
+                    "dense = every rank reads / writes its 1/N slice of all 9 planes from / to every peer",
+        }
     ms_per_step = dev_ms / K
     value = 1e3 / ms_per_step
     n_fw = max(float(live[2]), 1.0)
@@ -471,7 +491,7 @@ def run_ours(args):
                         "target from pinned host memory (this rank's band), gs2d_mse_ticket for this step (D2H of the "
                         "loss and the 48-byte device state) and gs2d_mse_wait (blocking) for the previous one; "
                         "serial_ms_per_step = blocking gs2d_set_target_rgba8 then gs2d_step(1, &mse)"},
-        "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "exchange": exchange,
         "exact_mode": {"value": 1e3 * K / exact_ms, "unit": "it/s", "ms_per_step": exact_ms / K,
                        "what": "GS2D_EXACT=1: blend kernels in the reference's operand order without FMA contraction "
                                "(image bit-identical to the CPU reference); same iterations, device-timed like `value`"},

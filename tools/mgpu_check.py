@@ -12,7 +12,7 @@ gs2d = importlib.import_module("2dgaussiansplatting_b200")
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-W, H, N, ITERS = 700, 520, 6000, 12
+W, H, N, ITERS = 700, 520, 6000, int(os.environ.get("MGPU_ITERS", "12"))
 target = np.rint(gs2d.synth_target(W, H, seed=3) * 255.0).astype(np.uint8)  # RGBA8: band-restricted upload path
 box = [gs2d.comm_unique_id() if rank == 0 else None]
 dist.broadcast_object_list(box, src=0)
@@ -24,7 +24,21 @@ with gs2d.Fitter(W, H, N, device=local) as fit:
     mse_n = fit.step(ITERS)[:, 0]
     s_n, a_n, b1_n, b2_n, it_n = fit.download()
     img_n = fit.image()
-ok = True
+    # Sparse exchange: a rank's OWN copy of the parameters must be exact for every Gaussian that passes its band test
+    # (k_preprocess: rows py +- (3 max(sx, sy) * 1.001 + 2) meet the band) - the others may be stale.
+    gs2d.set_tuning("GS2D_DOWNLOAD_LOCAL", 1)
+    s_loc = fit.download(with_adam=False)[0]
+    gs2d.set_tuning("GS2D_DOWNLOAD_LOCAL", 0)
+    t0, t1 = gs2d.band_rows((H + 15) // 16, rank, world)
+    hmax = 3.0 * np.maximum(np.abs(s_n["sx"]), np.abs(s_n["sy"])) * 1.001 + 2.0
+    in_band = ~((s_n["pos"][:, 1] + hmax < t0 * 16) | (s_n["pos"][:, 1] - hmax > t1 * 16))
+    same_loc = (s_loc.view(np.uint8).reshape(N, -1) == s_n.view(np.uint8).reshape(N, -1)).all(axis=1)
+    stale = int((~same_loc).sum())
+    bad_local = int((in_band & ~same_loc).sum())
+    rd, wr, sparse = fit.comm_traffic()
+    print(f"[rank {rank}] sparse={sparse} NVLink payload per iteration: read {rd / ITERS / 1e6:.2f} MB, written {wr / ITERS / 1e6:.2f} MB; "
+          f"own copy: {int(in_band.sum())} Gaussians in band, {stale} stale elsewhere, {bad_local} stale IN band (must be 0)", flush=True)
+ok = bad_local == 0
 if rank == 0:
     with gs2d.Fitter(W, H, N, device=local) as fit:
         fit.set_target_u8(target)
@@ -38,7 +52,7 @@ if rank == 0:
     am, a1 = a_n.view(np.float32), a_1.view(np.float32)
     da = np.abs(am - a1)
     print(f"comm mode (n_ranks, peer_memory) = {mode}; adam |diff| q99 {np.quantile(da, 0.99):.3e} vs scale {np.abs(a1).mean():.3e}")
-    ok = rel.max() < 1e-4 and np.quantile(d, 0.99) < 1e-2 and (b1_n, b2_n, it_n) == (b1_1, b2_1, it_1)
+    ok = ok and rel.max() < 1e-4 and np.quantile(d, 0.99) < 1e-2 and (b1_n, b2_n, it_n) == (b1_1, b2_1, it_1)
     ok = ok and np.quantile(da, 0.99) < 1e-3 * max(np.abs(a1).max(), 1e-30)
     want_peer = os.environ.get("GS2D_PEER_ADAM", "1") != "0"
     if os.environ.get("GS2D_EXPECT_PEER"):
@@ -49,7 +63,10 @@ tmin, tmax = t.clone(), t.clone()
 dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
 dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
 same = bool((tmin == tmax).all())
+okt = torch.tensor([1.0 if ok else 0.0], device="cuda")
+dist.all_reduce(okt, op=dist.ReduceOp.MIN)
 if rank == 0:
     print("replicated parameters identical on all ranks:", same)
+    print("all ranks ok:", bool(okt.item() > 0))
 dist.destroy_process_group()
-sys.exit(0 if (ok and same) else 1)
+sys.exit(0 if (okt.item() > 0 and same) else 1)
