@@ -508,6 +508,8 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	// + the 8-byte overflow counter of the slot binning, cleared together with the counters
 	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) ) );
 	CKC( cudaMalloc( &b.bucket_slots, sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * (size_t)g.nt_pad * g.n_slices ) );
+	// cleared once: k_rank loads a bucket's whole 16-byte slot row, of which only the first `count` slots were written
+	CKC( cudaMemset( b.bucket_slots, 0, sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * (size_t)g.nt_pad * g.n_slices ) );
 	CKC( cudaMalloc( &b.bucket_off, sizeof( unsigned ) * ( n_buckets + 4 ) ) );
 	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( n_buckets / 1024 + 16 ) ) );
 	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );

@@ -172,7 +172,9 @@ inline void DrawGrid( GridAxis, float, int, glm::u8vec3 ) {}
 inline void DrawXYZAxis( float ) {}
 inline void DrawCube( glm::vec3, glm::vec3, glm::u8vec3 ) {}
 inline void PrimBegin( PrimitiveMode, float = 1.0f ) {}
-inline void PrimVertex( glm::vec3, glm::u8vec3 ) {}
+// recorded (frame, position, colour) when PR_PRIMS names a file: the overlay main() draws per splat (main.cpp:442-476),
+// the golden data of gs2d_overlay_geometry (tests/golden/make_overlay_golden.py)
+void PrimVertex( glm::vec3 p, glm::u8vec3 c );
 inline void PrimEnd() {}
 inline void DrawText( glm::vec3, std::string, float = 16.0f ) {}
 inline void BeginImGui() {}

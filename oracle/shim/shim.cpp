@@ -33,6 +33,28 @@ double GetElapsedTime()
 }
 double GetFrameRate() { return 0.0; }
 
+// PR_PRIMS=file: every PrimVertex of the frames listed in PR_PRIMS_FRAMES (comma separated, default "0") is appended as
+// { int32 frame; float x, y, z; uint8 r, g, b, 0 } (20 bytes)
+void PrimVertex( glm::vec3 p, glm::u8vec3 c )
+{
+	static const char* path = getenv( "PR_PRIMS" );
+	if( !path )
+		return;
+	static FILE* fp = fopen( path, "wb" );
+	static std::string frames = std::string( "," ) + env_or( "PR_PRIMS_FRAMES", "0" ) + ",";
+	const int frame = g_frames - 1; // NextFrame() has already counted the frame being drawn
+	if( !fp || frames.find( "," + std::to_string( frame ) + "," ) == std::string::npos )
+		return;
+	struct
+	{
+		int32_t frame;
+		float x, y, z;
+		uint8_t r, g, b, pad;
+	} rec = { frame, p.x, p.y, p.z, c.x, c.y, c.z, 0 };
+	fwrite( &rec, sizeof( rec ), 1, fp );
+	fflush( fp );
+}
+
 bool NextFrame()
 {
 	static int iters = atoi( env_or( "PR_ITERS", "20" ) );

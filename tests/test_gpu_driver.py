@@ -57,6 +57,30 @@ def test_driver_stdout_equals_reference_stdout(golden_dir, tmp_path):
     assert len(open(csv).read().strip().splitlines()) == 1 + 1024
 
 
+def test_reference_main_with_the_loop_body_replaced_by_gs2d_step(golden_dir, tmp_path):
+    """The drop-in boundary exercised from the reference's OWN main(): oracle/_ref/patched_main is /root/reference's
+    main.cpp with lines 414-809 cut out and gs2d_step() called in their place (oracle/patched/make_patched.py applies
+    INTEGRATION.md's patch to a copy at build time), compiled against the same headless shim as oracle level 0 and
+    linked with -lgs2d. Its stdout must be the unmodified reference's (tests/golden/c1_mse.txt)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "patched_main")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/patched_main not built (needs /root/reference: make -C oracle patched)")
+    write_target_ppm(golden_dir, "c1", str(tmp_path / "c1.ppm"))  # the shim's stb_image decodes PPM like the JPEG: same pixels
+    ref = parse(open(os.path.join(golden_dir, "c1_mse.txt")).read().strip().splitlines()[:60])
+    for exact in ("1", "0"):
+        env = dict(os.environ, PR_DATA=str(tmp_path), PR_IMAGE="c1.ppm", PR_ITERS="60", GS2D_EXACT=exact)
+        r = subprocess.run([exe], capture_output=True, text=True, timeout=300, env=env)
+        assert r.returncode == 0, r.stderr[-2000:]
+        got = parse(r.stdout.strip().splitlines())
+        assert [g[0] for g in got] == list(range(60))
+        rel = np.array([abs(g[1] - e[1]) / e[1] for g, e in zip(got, ref)])
+        if exact == "1":
+            assert r.stdout.splitlines()[0] == open(os.path.join(golden_dir, "c1_mse.txt")).readline().rstrip("\n")
+        else:
+            assert rel[0] < 2e-6, rel[0]
+        assert rel[:50].max() < 1e-4 and rel.max() < 2e-3, rel.max()
+
+
 def test_driver_restart_and_opacity_events(golden_dir, tmp_path):
     """The "Restart" button re-runs init(): the loss curve starts over; the opacity checkbox changes the fit."""
     ppm = str(tmp_path / "c1.ppm")

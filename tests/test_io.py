@@ -97,3 +97,43 @@ def test_overlay_geometry_matches_reference_formulas():
         d = ell[i].astype(np.float64) - s["pos"][i]
         m = np.einsum("ki,ij,kj->k", d, np.linalg.inv(cov), d)
         assert np.allclose(m, 1.0, atol=2e-3)
+
+
+def test_overlay_geometry_matches_the_reference_draw_calls(golden_dir):
+    """gs2d_overlay_geometry against the PrimVertex calls of the UNMODIFIED reference (main.cpp:442-476), recorded by
+    the level-0 shim in frames 0 and 6 of the default configuration (tests/golden/make_overlay_golden.py). The
+    Gaussians of frame 6 come from six iterations of the level-1 oracle (bit-identical to level 0, test_oracle.py)."""
+    import oracle_binding as ob
+
+    g = np.load(os.path.join(golden_dir, "c1_overlay.npz"))
+    rgb = np.load(os.path.join(golden_dir, "c1_target_rgb8.npz"))["rgb"]
+    h, w, _ = rgb.shape
+    target = ob.u8_to_target(np.concatenate([rgb, np.full((h, w, 1), 255, np.uint8)], axis=2))
+    st = ob.State(w, h, 1024)
+    done = 0
+    for k, frame in enumerate(g["frames"]):
+        while done < frame:
+            st.step(target)
+            done += 1
+        s = st.splats
+        rec, ell = gs2d.overlay_geometry(s, nvtx=16)
+        xy = g["xy"][k].astype(np.float64)            # [1024, 46, 2], y flipped for GL (main.cpp:447)
+        ref = xy * np.array([1.0, -1.0])              # back to image coordinates
+        c = s["pos"].astype(np.float64)
+        tol = dict(rtol=0, atol=2e-5)                 # coordinates of a few hundred: ~1 ulp
+        assert np.allclose(ref[:, 0], c, **tol) and np.allclose(ref[:, 2], c, **tol)
+        assert np.allclose(ref[:, 1], c + rec["axis0"], **tol)          # eigen axis of the larger eigenvalue
+        assert np.allclose(ref[:, 3], c + rec["axis1"], **tol)
+        # ellipse: vertices 4 + 2 i are the segment starts E_i, i = 0..16 (CircleGenerator recurrence, prp.hpp:276-313)
+        assert np.allclose(ref[:, 4:38:2], ell, **tol)
+        # segment ends: E_{i+1}
+        assert np.allclose(ref[:, 5:37:2], ell[:, 1:], **tol)
+        # 1-sigma box: (-hx,-hy) (hx,-hy) (hx,hy) (-hx,hy) in GL coordinates around (x, -y)
+        hx, hy = rec["half_extent"][:, 0].astype(np.float64), rec["half_extent"][:, 1].astype(np.float64)
+        gl = xy[:, 38:46:2] - xy[:, 0][:, None, :]
+        want = np.stack([np.stack([-hx, -hy], 1), np.stack([hx, -hy], 1), np.stack([hx, hy], 1), np.stack([-hx, hy], 1)], 1)
+        assert np.allclose(gl, want, **tol)
+        # colours: white / 230 axes, splat colour * 255 truncated, 128 box (main.cpp:446-470)
+        col = g["rgb"][k]
+        assert (col[:, 0:3] == 255).all() and (col[:, 3] == 230).all() and (col[:, 38:] == 128).all()
+        assert np.array_equal(col[:, 4], (s["color"] * np.float32(255.0)).astype(np.uint32).astype(np.uint8))
