@@ -298,7 +298,7 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	const bool optimised = pl != PL_OP || hp.optimize_opacity;
 	// which ranks may hold a non-zero gradient for this quad (their band test passed one of its Gaussians)
 	unsigned tmask = ( 1u << NR ) - 1u;
-	if( pp.sparse && pp.sum_all )
+	if( pp.sparse && pp.sum_all && !( pp.probe & 4 ) )
 	{
 		unsigned w[NR];
 #pragma unroll
@@ -317,7 +317,8 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 			float4 part[NR];
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
-				part[r] = ( ( tmask >> r ) & 1u ) ? ld_sys4( pp.grads[r] + o ) : make_float4( 0.f, 0.f, 0.f, 0.f ); // in flight together
+				part[r] = ( ( ( tmask >> r ) & 1u ) && !( ( pp.probe & 1 ) && r != pp.rank ) ) ? ld_sys4( pp.grads[r] + o )
+				                                                                              : make_float4( 0.f, 0.f, 0.f, 0.f ); // in flight together
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
 			{
@@ -342,9 +343,12 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 		float4 m = *reinterpret_cast<float4*>( adam_m + o );
 		float4 v = *reinterpret_cast<float4*>( adam_v + o );
 		float mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
+		if( !( pp.probe & 8 ) )
+		{
 #pragma unroll
-		for( int k = 0; k < 4; k++ )
-			pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
+			for( int k = 0; k < 4; k++ )
+				pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
+		}
 		*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
 		*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
 	}
@@ -395,7 +399,7 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	{
 #pragma unroll
 		for( int r = 0; r < NR; r++ )
-			if( ( send >> r ) & 1u )
+			if( ( ( send >> r ) & 1u ) && !( ( pp.probe & 2 ) && r != pp.rank ) )
 				*reinterpret_cast<float4*>( pp.params[r] + o ) = out;
 	}
 	if( pp.traffic )

@@ -1593,8 +1593,9 @@ static int setup_peer_update( gs2d_ctx* c )
 		pp.touch[r] = (const unsigned*)ptr[5];
 	}
 	pp.sparse = gs2d_tune( "GS2D_PEER_SPARSE", 1 ) ? 1 : 0;
+	pp.probe = gs2d_tune( "GS2D_PEER_PROBE", 0 );
 	pp.reach_prev = c->reach_prev;
-	pp.traffic = c->peer_traffic;
+	pp.traffic = gs2d_tune( "GS2D_PEER_TRAFFIC", 1 ) ? c->peer_traffic : nullptr;
 	pp.band_tile_rows = ( c->g.tiles_y + n - 1 ) / n; // set_band
 	// agree: the peer path is used only if every rank mapped every peer
 	int* flag = reinterpret_cast<int*>( dev );

@@ -222,6 +222,8 @@ struct PeerPtrs
 	unsigned long long* traffic; // [2] 16-byte quads read from / written to peers over NVLink (running sums)
 	int sparse;
 	int band_tile_rows;        // tile rows per rank (set_band)
+	int probe;                 // developer timing knob GS2D_PEER_PROBE (results are WRONG when set): 1 no remote gradient
+	                           // loads, 2 no remote parameter stores, 4 no touch-bitmap loads, 8 no Adam arithmetic
 	// mailboxes for the flag barriers (one per rank, mapped everywhere): see PeerMailbox
 	unsigned char* mbox[GS2D_MAX_RANKS];
 };
