@@ -296,6 +296,31 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	const int pl = blockIdx.y;
 	const size_t o = (size_t)pl * g.n_pad + i4;
 	const bool optimised = pl != PL_OP || hp.optimize_opacity;
+	// Everything this thread reads from its OWN memory is requested first, so that it is in flight while the two
+	// dependent rounds of NVLink loads below (touch words, then gradient quads) make their way: with the loads in
+	// program order behind them the kernel was a chain of four memory latencies per wave (measured: 40 us at 8 ranks
+	// with every peer access switched off, where the arithmetic and the HBM traffic account for 8).
+	const float* own = pp.params[pp.rank];
+	const float4 p = __ldcs( reinterpret_cast<const float4*>( own + o ) );
+	float4 m = make_float4( 0.f, 0.f, 0.f, 0.f ), v = m;
+	if( optimised )
+	{
+		m = __ldcs( reinterpret_cast<const float4*>( adam_m + o ) );
+		v = __ldcs( reinterpret_cast<const float4*>( adam_v + o ) );
+	}
+	float4 rpy = m, rsx = m, rsy = m;
+	unsigned reach_last = 0;
+	const int par = st->iteration & 1; // k_advance has run: the parity of the iteration being finished
+	const size_t nq = (size_t)g.n_pad / 4;
+	if( pp.sparse )
+	{
+		rpy = *reinterpret_cast<const float4*>( own + (size_t)PL_PY * g.n_pad + i4 );
+		rsx = *reinterpret_cast<const float4*>( own + (size_t)PL_SX * g.n_pad + i4 );
+		rsy = *reinterpret_cast<const float4*>( own + (size_t)PL_SY * g.n_pad + i4 );
+		reach_last = pp.reach_prev[(size_t)par * nq + q];
+	}
+	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
+	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
 	// which ranks may hold a non-zero gradient for this quad (their band test passed one of its Gaussians)
 	unsigned tmask = ( 1u << NR ) - 1u;
 	if( pp.sparse && pp.sum_all && !( pp.probe & 4 ) )
@@ -334,14 +359,9 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 			gv[0] = t.x, gv[1] = t.y, gv[2] = t.z, gv[3] = t.w;
 		}
 	}
-	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
-	const float wmax = xsub( (float)g.W, 1.0f ), hmax = xsub( (float)g.H, 1.0f );
-	const float4 p = *reinterpret_cast<const float4*>( pp.params[pp.rank] + o );
 	float pv[4] = { p.x, p.y, p.z, p.w };
 	if( optimised )
 	{
-		float4 m = *reinterpret_cast<float4*>( adam_m + o );
-		float4 v = *reinterpret_cast<float4*>( adam_v + o );
 		float mv[4] = { m.x, m.y, m.z, m.w }, vv[4] = { v.x, v.y, v.z, v.w };
 		if( !( pp.probe & 8 ) )
 		{
@@ -349,8 +369,8 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 			for( int k = 0; k < 4; k++ )
 				pv[k] = adam_one( pv[k], gv[k], mv[k], vv[k], hp.lr, hp.beta1, hp.beta2, hp.eps, om_b1t, om_b2t );
 		}
-		*reinterpret_cast<float4*>( adam_m + o ) = make_float4( mv[0], mv[1], mv[2], mv[3] );
-		*reinterpret_cast<float4*>( adam_v + o ) = make_float4( vv[0], vv[1], vv[2], vv[3] );
+		__stcs( reinterpret_cast<float4*>( adam_m + o ), make_float4( mv[0], mv[1], mv[2], mv[3] ) );
+		__stcs( reinterpret_cast<float4*>( adam_v + o ), make_float4( vv[0], vv[1], vv[2], vv[3] ) );
 	}
 	bool bad = false;
 #pragma unroll
@@ -378,20 +398,13 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	unsigned send = ( 1u << NR ) - 1u;
 	if( pp.sparse )
 	{
-		const float* own = pp.params[pp.rank];
-		const float4 py = *reinterpret_cast<const float4*>( own + (size_t)PL_PY * g.n_pad + i4 );
-		const float4 sx = *reinterpret_cast<const float4*>( own + (size_t)PL_SX * g.n_pad + i4 );
-		const float4 sy = *reinterpret_cast<const float4*>( own + (size_t)PL_SY * g.n_pad + i4 );
-		// these may be the values before or after this very kernel's update of the three planes (their threads run
-		// concurrently): the slack covers one Adam step either way
+		// rpy / rsx / rsy may be the values before or after this very kernel's update of the three planes (their
+		// threads run concurrently): the slack covers one Adam step either way
 		const int per_px = pp.band_tile_rows * GS2D_TILE;
 		const float slack = 1.0f + 3.0f * hp.lr * 1.001f + hp.lr;
-		const unsigned now = reach_mask( py.x, sx.x, sy.x, per_px, NR, slack ) | reach_mask( py.y, sx.y, sy.y, per_px, NR, slack ) |
-		                     reach_mask( py.z, sx.z, sy.z, per_px, NR, slack ) | reach_mask( py.w, sx.w, sy.w, per_px, NR, slack );
-		const int par = st->iteration & 1; // k_advance has run: the parity of the iteration being finished
-		const size_t nq = (size_t)g.n_pad / 4;
-		const unsigned prev = pp.reach_prev[(size_t)par * nq + q];
-		send = now | prev | ( 1u << pp.rank );
+		const unsigned now = reach_mask( rpy.x, rsx.x, rsy.x, per_px, NR, slack ) | reach_mask( rpy.y, rsx.y, rsy.y, per_px, NR, slack ) |
+		                     reach_mask( rpy.z, rsx.z, rsy.z, per_px, NR, slack ) | reach_mask( rpy.w, rsx.w, rsy.w, per_px, NR, slack );
+		send = now | reach_last | ( 1u << pp.rank );
 		if( pl == 0 )
 			pp.reach_prev[(size_t)( par ^ 1 ) * nq + q] = (unsigned char)now;
 	}
@@ -504,6 +517,12 @@ int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s )
 	if( g.n_total == 0 )
 		return 0;
 	k_init_reference<<<( g.n_total + 255 ) / 256, 256, 0, s>>>( g, b.params );
+	return 1;
+}
+__global__ void k_u8_lut( float* __restrict__ lut ) { lut[threadIdx.x] = xdiv( (float)threadIdx.x, 255.0f ); }
+int launch_u8_lut( float* lut, cudaStream_t s )
+{
+	k_u8_lut<<<1, 256, 0, s>>>( lut );
 	return 1;
 }
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s )

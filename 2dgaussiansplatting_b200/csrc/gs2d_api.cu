@@ -132,7 +132,8 @@ struct gs2d_ctx
 	size_t ustage_bytes = 0;
 	cudaEvent_t copy_done[2] = { nullptr, nullptr }, convert_done[2] = { nullptr, nullptr };
 	int ustage_next = 0;
-	int pending_buf = -1, pending_image = 0; // an uploaded target that has not been converted yet
+	int pending_buf = -1, pending_image = 0; // an uploaded target that has not been taken over yet
+	std::vector<char> img_fmt;               // per image: 0 no target yet (zeros), 1 float32, 2 RGBA8 (target_store_u8)
 	size_t pending_px0 = 0, pending_npx = 0;
 
 	// One iteration captured as a CUDA graph (single GPU, profiling off): 13 dependent nodes replayed per iteration
@@ -375,7 +376,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->side.ev_join )
 		cudaEventDestroy( c->side.ev_join );
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
-	                 b.rowrec,     b.rowtab,
+	                 b.rowrec,     b.rowtab,     b.target8,    b.u8_lut,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->peer_traffic };
@@ -456,8 +457,16 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 		}                                                                                                             \
 	} while( 0 )
 	CKC( cudaSetDevice( device ) );
-	CKC( cudaStreamCreateWithFlags( &c->stream, cudaStreamNonBlocking ) );
-	CKC( cudaStreamCreateWithFlags( &c->side.stream, cudaStreamNonBlocking ) );
+	{
+		// The side stream (k_row_table: pure arithmetic, 31 000 short blocks) gets the LOWEST priority and the main
+		// stream the highest: the binning kernels that run beside it (scan / place / rank: few instructions, long
+		// waits on L2) then take the SM slots they need as soon as row-table blocks retire, and the row table fills
+		// what is left - with equal priorities the kernel launched first simply occupies every SM.
+		int prio_lo = 0, prio_hi = 0;
+		cudaDeviceGetStreamPriorityRange( &prio_lo, &prio_hi );
+		CKC( cudaStreamCreateWithPriority( &c->stream, cudaStreamNonBlocking, prio_hi ) );
+		CKC( cudaStreamCreateWithPriority( &c->side.stream, cudaStreamNonBlocking, prio_lo ) );
+	}
 	CKC( cudaEventCreateWithFlags( &c->side.ev_fork, cudaEventDisableTiming ) );
 	CKC( cudaEventCreateWithFlags( &c->side.ev_join, cudaEventDisableTiming ) );
 	prepare_forward_pdl();
@@ -514,6 +523,11 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.scan_sums, sizeof( unsigned ) * ( n_buckets / 1024 + 16 ) ) );
 	CKC( cudaMalloc( &b.tile_range, sizeof( uint2 ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.target, sizeof( float4 ) * n_px ) );
+	CKC( cudaMalloc( &b.u8_lut, sizeof( float ) * 256 ) );
+	c->launches += launch_u8_lut( b.u8_lut, c->stream );
+	g.u8_lut = b.u8_lut;
+	g.target_u8 = 0;
+	c->img_fmt.assign( (size_t)n_images, 0 );
 	CKC( cudaMalloc( &b.image, sizeof( float4 ) * n_px ) );
 	CKC( cudaMalloc( &b.loss_partial, sizeof( double ) * (size_t)g.n_tiles_total ) );
 	CKC( cudaMalloc( &b.tile_done, sizeof( unsigned ) * (size_t)g.n_tiles_total ) );
@@ -578,9 +592,53 @@ extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgb
 	rc = ensure_staging( c, bytes );
 	if( rc )
 		return rc;
+	if( c->g.target_u8 )
+	{
+		// the context has been reading RGBA8 targets: from now on it reads float32 ones, the 8-bit images converted
+		// once (u8 / 255.0f, prp.cpp:796-807)
+		for( int i = 0; i < c->g.n_images; i++ )
+			if( c->img_fmt[(size_t)i] == 2 )
+			{
+				c->launches += launch_u8_to_target( reinterpret_cast<const uint8_t*>( c->b.target8 + (size_t)i * n_px ),
+				                                    c->b.target + (size_t)i * n_px, n_px, c->stream );
+				c->img_fmt[(size_t)i] = 1;
+			}
+		c->g.target_u8 = 0;
+	}
 	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice,
 	                     c->stream ) );
 	CK( cudaStreamSynchronize( c->stream ) );
+	c->img_fmt[(size_t)image] = 1;
+	return check_launch( c );
+}
+
+// An RGBA8 target (rows [px0, px0 + npx) of `image`, already on the device at dev_src) becomes the image's target.
+// As long as no image of the context has a float32 target, the 8-bit pixels are kept as they are and the blend kernels
+// convert on the fly (Geometry::target_u8): one device-to-device copy of 4 bytes per pixel instead of a conversion
+// pass that reads 4 and writes 16. Otherwise they are converted into the float32 target as before.
+static int target_store_u8( gs2d_ctx* c, int image, const uint8_t* dev_src, size_t px0, size_t npx )
+{
+	const size_t n_px = (size_t)c->g.W * c->g.H;
+	bool any_float = false;
+	for( char f : c->img_fmt )
+		any_float = any_float || f == 1;
+	if( any_float )
+	{
+		if( npx )
+			c->launches += launch_u8_to_target( dev_src, c->b.target + (size_t)image * n_px + px0, npx, c->stream );
+		c->img_fmt[(size_t)image] = 1;
+		return check_launch( c );
+	}
+	if( !c->b.target8 )
+	{
+		const size_t bytes = sizeof( uchar4 ) * n_px * (size_t)c->g.n_images;
+		CK( cudaMalloc( &c->b.target8, bytes ) );
+		CK( cudaMemsetAsync( c->b.target8, 0, bytes, c->stream ) ); // images without a target: zeros, as in the float32 buffer
+	}
+	if( npx )
+		CK( cudaMemcpyAsync( c->b.target8 + (size_t)image * n_px + px0, dev_src, npx * 4, cudaMemcpyDeviceToDevice, c->stream ) );
+	c->img_fmt[(size_t)image] = 2;
+	c->g.target_u8 = 1;
 	return GS2D_OK;
 }
 
@@ -598,7 +656,7 @@ static void target_rows( const gs2d_ctx* c, size_t* px0, size_t* npx )
 	*npx = (size_t)( y1 - y0 ) * c->g.W;
 }
 
-// enqueue the conversion of an asynchronously uploaded target on the main stream (before the next forward)
+// take an asynchronously uploaded target over on the main stream (before the next forward)
 static int apply_pending_target( gs2d_ctx* c )
 {
 	if( c->pending_buf < 0 )
@@ -606,10 +664,9 @@ static int apply_pending_target( gs2d_ctx* c )
 	const int k = c->pending_buf;
 	c->pending_buf = -1;
 	CK( cudaStreamWaitEvent( c->stream, c->copy_done[k], 0 ) );
-	if( c->pending_npx )
-		c->launches += launch_u8_to_target( c->ustage[k],
-		                                    c->b.target + (size_t)c->pending_image * c->g.W * c->g.H + c->pending_px0,
-		                                    c->pending_npx, c->stream );
+	int rc = target_store_u8( c, c->pending_image, c->ustage[k], c->pending_px0, c->pending_npx );
+	if( rc )
+		return rc;
 	CK( cudaEventRecord( c->convert_done[k], c->stream ) );
 	return check_launch( c );
 }
@@ -631,9 +688,10 @@ extern "C" int gs2d_set_target_rgba8( gs2d_ctx* c, int image, const uint8_t* rgb
 	if( npx )
 	{
 		CK( cudaMemcpyAsync( c->dstage, h2d_source( c, rgba + px0 * 4, bytes ), bytes, cudaMemcpyHostToDevice, c->stream ) );
-		c->launches += launch_u8_to_target( (const uint8_t*)c->dstage,
-		                                    c->b.target + (size_t)image * c->g.W * c->g.H + px0, npx, c->stream );
 	}
+	rc = target_store_u8( c, image, (const uint8_t*)c->dstage, px0, npx );
+	if( rc )
+		return rc;
 	CK( cudaStreamSynchronize( c->stream ) );
 	return check_launch( c );
 }

@@ -183,7 +183,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		{
 			const size_t pix = ( (size_t)img * g.H + y ) * g.W + x;
 			const float4 fin = PDL ? __ldcg( image + pix ) : image[pix]; // PDL: written by a grid that is still running
-			const float4 ref = target[pix];
+			const float4 ref = load_target( g, target, pix );
 			dLr[j] = xsub( fin.x, ref.x );
 			dLg[j] = xsub( fin.y, ref.y );
 			dLb[j] = xsub( fin.z, ref.z );
@@ -432,7 +432,8 @@ static void launch_backward_as( dim3 grid, const Geometry& g, const Buffers& b, 
 	cfg.attrs = attr;
 	cfg.numAttrs = PDL ? 1 : 0;
 	cudaLaunchKernelEx( &cfg, kernel, g, (const SplatRec*)b.rec, (const unsigned*)b.vals[sorted_buf],
-	                    (const uint2*)b.tile_range, (const float4*)b.target, (const float4*)b.image,
+	                    (const uint2*)b.tile_range,
+	                    g.target_u8 ? reinterpret_cast<const float4*>( b.target8 ) : (const float4*)b.target, (const float4*)b.image,
 	                    (const unsigned*)b.cover, b.grads, slots, (const DevState*)b.state,
 	                    (const unsigned*)( PDL ? b.tile_done : nullptr ) );
 }

@@ -224,7 +224,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 		if( x < g.W && y < g.H )
 		{
 			const size_t pix = ( (size_t)img * g.H + y ) * g.W + x;
-			const float4 ref = target[pix];
+			const float4 ref = load_target( g, target, pix );
 			image[pix] = make_float4( Cr[j], Cg[j], Cb[j], 1.0f );
 			const float dr = xmul( xsub( Cr[j], ref.x ), 255.0f ), dg = xmul( xsub( Cg[j], ref.y ), 255.0f ),
 			            db = xmul( xsub( Cb[j], ref.z ), 255.0f );
@@ -263,7 +263,8 @@ void prepare_forward_pdl()
 template <int MINB, bool COUNT, bool PDL, bool EXACT>
 static void launch_forward_as( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, int vh, cudaStream_t s )
 {
-	k_forward<MINB, COUNT, PDL, EXACT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range, b.target, b.image,
+	k_forward<MINB, COUNT, PDL, EXACT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
+	                                                       g.target_u8 ? reinterpret_cast<const float4*>( b.target8 ) : b.target, b.image,
 	                                                       b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state,
 	                                                       COUNT ? vh : 0, PDL ? b.tile_done : nullptr, b.rowtab, b.rowrec );
 }

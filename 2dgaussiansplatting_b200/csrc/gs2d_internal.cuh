@@ -113,6 +113,12 @@ struct Geometry
 	int nt_pad;              // n_tiles_total rounded up to a multiple of 4
 	int n_slices, slice_size; // index slices of an image's splats: slice = i / slice_size, slice_size <= 65535
 	float min_throughput;    // MIN_THROUGHPUT, main.cpp:8
+	// Target format (not geometry, but it travels to the same kernels and into the same graph key): 1 = the blend
+	// kernels read the target as RGBA8 (Buffers::target8, the reference's ingest format, prp.cpp:179-193) and convert
+	// with u8_lut[c] == (float)c / 255.0f (prp.cpp:796-807) - 4 bytes per pixel instead of 16, and no conversion pass
+	// per uploaded target; 0 = RGBA float32 (Buffers::target, == imageRef).
+	int target_u8;
+	const float* u8_lut;     // [256]
 };
 
 #include "gs2d_footprint.cuh" // contraction-free helpers, exp_approx, exact row footprint, tile-row spans
@@ -154,6 +160,8 @@ struct Buffers
 	unsigned long long capacity;
 	uint2* tile_range;        // [n_tiles_total]
 	float4* target;           // [n_images][H][W]
+	uchar4* target8;          // [n_images][H][W] RGBA8 targets (allocated at the first 8-bit upload; Geometry::target_u8)
+	float* u8_lut;            // [256] c / 255.0f
 	float4* image;            // [n_images][H][W]
 	double* loss_partial;     // [n_tiles_total]
 	unsigned* tile_done;      // [n_tiles_total] forward -> backward tile flags of the PDL overlap (gs2d_blend.cuh)
@@ -169,6 +177,17 @@ struct Buffers
 
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
+int launch_u8_lut( float* lut, cudaStream_t s );
+// the reference pixel of the loss / of dL/dC (imageRef, main.cpp:616, :800) in either target format
+__device__ __forceinline__ float4 load_target( const Geometry& g, const float4* __restrict__ target, size_t pix )
+{
+	if( g.target_u8 )
+	{
+		const uchar4 c = reinterpret_cast<const uchar4*>( target )[pix];
+		return make_float4( __ldg( g.u8_lut + c.x ), __ldg( g.u8_lut + c.y ), __ldg( g.u8_lut + c.z ), 1.0f );
+	}
+	return target[pix];
+}
 // use_slots: slot binning unless the context has switched it off for now (gs2d_ctx::slot_binning) or GS2D_SLOTS=0
 // side: a second stream the row table kernel runs on, concurrently with the scan / place / rank kernels (fork and
 // join through ev_fork / ev_join; also inside a stream capture); nullptr: everything on s

@@ -1,0 +1,13 @@
+#!/bin/bash
+# round 2 profiles: full ncu capture of one launch of each hot kernel, and the launch list of the bench command
+TAG=${1:-r2}; OUT=gpurun_out; mkdir -p $OUT
+export GS2D_STATS=0
+timeout 300 python tools/quick_time.py 4096 1000000 3 > $OUT/${TAG}_quick.log 2>&1 &&
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_forward|k_backward|k_row_table|k_preprocess|k_rank|k_adam|k_scan_local' -s 21 -c 7 -f \
+    -o $OUT/${TAG}_kernels python tools/quick_time.py 4096 1000000 3 > $OUT/${TAG}_ncu_full.log 2>&1
+echo "ncu full exit $?"; cat $OUT/${TAG}_quick.log
+unset GS2D_STATS
+timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_plain.json 2> $OUT/${TAG}_plain.err &&
+timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $OUT/${TAG}_launches_bench.csv \
+    python bench.py --steps 3 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_bench.log 2>&1
+echo "launch list exit $?"; wc -l $OUT/${TAG}_launches_bench.csv

@@ -15,6 +15,8 @@ with gs2d.Fitter(S, S, N, n_images=B) as fit:
     for i in range(B):
         fit.set_target_u8(tgt, image=i)
     fit.restart()
+    if os.environ.get('GS2D_OPT_OPACITY') == '1':  # the "Optimize opacity" checkbox (main.cpp:825): k_backward<.., OPACITY = true>
+        fit.optimize_opacity = True
     if os.environ.get('GS2D_BAND'):  # "r/n": time one rank's band of an n-rank run on a single GPU (no all-reduce)
         r, n = map(int, os.environ['GS2D_BAND'].split('/'))
         fit.set_band(r, n)
