@@ -419,6 +419,71 @@ def test_forward_backward_overlap_equals_the_serialised_launch():
         assert np.isfinite(img).all() and (img[..., 3] == 1.0).all(), key
 
 
+def test_overlap_with_mostly_empty_tiles():
+    """empty tiles' backward warps leave without waiting for their tile flag, so the ordering of whatever
+    follows the backward grid (k_finalize_loss sums the loss partials of ALL forward warps) rests on the
+    griddepcontrol.wait every backward warp ends with. 60 Gaussians on 1024 x 1024 (4096 tiles, > 95 % of them
+    empty): the loss of every iteration with the overlap on must equal the serialised launch's."""
+    W = H = 1024
+    n = 60
+    rng = np.random.default_rng(8)
+    splats = random_splats(rng, W, H, n, smin=3, smax=12)
+    target = gs2d.synth_target(W, H, seed=6)
+    runs = {}
+    try:
+        for pdl in (0, 1):
+            for graph in (1, 0):
+                gs2d.set_tuning("GS2D_PDL", pdl)
+                gs2d.set_tuning("GS2D_GRAPH", graph)
+                with gs2d.Fitter(W, H, n) as fit:
+                    fit.set_target(target)
+                    fit.upload(splats)
+                    runs[(pdl, graph)] = fit.step(40)[:, 0]
+    finally:
+        gs2d.set_tuning("GS2D_PDL", 1)
+        gs2d.set_tuning("GS2D_GRAPH", 1)
+    ref = runs[(0, 0)]
+    assert ref[0] > 0
+    for key, mse in runs.items():
+        assert mse[0] == ref[0], key
+        assert np.max(np.abs(mse - ref) / ref) < 1e-6, key
+
+
+def test_nonfinite_freezes_the_fit_like_the_reference_abort():
+    """The reference abort()s in the iteration whose Adam step produced a non-finite parameter, after the whole update
+    loop and before that iteration's printf (main.cpp:752-785, :807). The device mirrors it: the iteration counter stays
+    at the failing iteration's index + 1 and nothing enqueued behind it changes the state."""
+    W, H, n = 64, 64, 16
+    s = ob.init_splats(W, H, n)
+    target = gs2d.synth_target(W, H)
+    with gs2d.Fitter(W, H, n) as fit:
+        fit.set_target(target)
+        fit.upload(s)
+        fit.step(3)
+        good, _, _, _, it = fit.download()
+        assert it == 3
+        bad = good.copy()
+        bad["rot"][5] = np.nan  # no footprint; Adam leaves the NaN in place: flagged by the next step (main.cpp:776-779)
+        fit.upload(bad, iteration=3)
+        with pytest.raises(gs2d.Gs2dError) as e:
+            fit.step(10)  # ten iterations enqueued at once: only the first may take effect
+        assert e.value.code == gs2d.GS2D_ERR_NONFINITE
+        s1, _, b1, b2, it1 = fit.download()
+        assert it1 == 4  # frozen at the failing iteration's index + 1
+        with pytest.raises(gs2d.Gs2dError):
+            fit.step(5)
+        s2, _, _, _, it2 = fit.download()
+        assert it2 == 4 and s2.tobytes() == s1.tobytes()
+        # the parameters are the ones one Adam step from `bad` gives (the reference holds them when it aborts)
+        o = ob.State(W, H, splats=bad)
+        o.step(target)
+        ok = np.isfinite(o.splats.view(np.float32)).reshape(n, 9).all(axis=1)
+        assert np.quantile(np.abs(s1[ok].view(np.float32) - o.splats[ok].view(np.float32)), 0.99) <= 2e-4
+        # a fresh state un-freezes the context
+        fit.upload(good, iteration=3)
+        assert fit.step(2).shape == (2, 1) and fit.download()[4] == 5
+
+
 def test_nonfinite_is_reported_not_aborted():
     W, H = 64, 64
     s = ob.init_splats(W, H, 8)
