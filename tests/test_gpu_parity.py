@@ -621,6 +621,36 @@ def crop_check(fit, splats, rgba8, window, mode, label):
     return img, g, st
 
 
+def test_target_formats_can_be_mixed():
+    """RGBA8 targets are read by the blend kernels as they are (4 bytes per pixel, converted through a 256-entry table
+    of c / 255.0f, prp.cpp:796-807) as long as no image of the context has a float32 target; the first float32 upload
+    converts the 8-bit images once and the context carries on in float32. All routes must give the same fit."""
+    W, H, n = 150, 110, 300
+    rng = np.random.default_rng(4)
+    t8 = [rng.integers(0, 256, (H, W, 4), dtype=np.uint8) for _ in range(2)]
+    tf = [ob.u8_to_target(t) for t in t8]
+    curves = []
+    for route in ("u8 u8", "f32 f32", "u8 then f32", "f32 then u8", "u8, step, then f32 for the other image"):
+        with gs2d.Fitter(W, H, n, n_images=2) as fit:
+            if route == "u8 u8":
+                fit.set_target_u8(t8[0], 0); fit.set_target_u8(t8[1], 1)
+            elif route == "f32 f32":
+                fit.set_target(tf[0], 0); fit.set_target(tf[1], 1)
+            elif route == "u8 then f32":
+                fit.set_target_u8(t8[0], 0); fit.set_target(tf[1], 1)
+            elif route == "f32 then u8":
+                fit.set_target(tf[0], 0); fit.set_target_u8(t8[1], 1)
+            else:
+                fit.set_target_u8(t8[0], 0); fit.set_target_u8(t8[0], 1)
+                fit.restart(); fit.step(2)
+                fit.set_target(tf[1], 1)
+            fit.restart()
+            curves.append(fit.step(6))
+    for c in curves[1:]:
+        assert c[0, 0] == curves[0][0, 0] and c[0, 1] == curves[0][0, 1]
+        assert np.allclose(c, curves[0], rtol=1e-7, atol=0)
+
+
 def test_full_size_crop_against_oracle(mode):
     """BASELINE config 3 size (4096^2, 1 M Gaussians): forward and backward against the oracle on a 256x192 window."""
     W = H = 4096
