@@ -259,6 +259,9 @@ __global__ void __launch_bounds__( 32 ) k_peer_barrier2( PeerPtrs pp, unsigned l
 // the peer pointers live in registers and all NR loads are issued before the first add). Gradients are summed in
 // rank order (deterministic), and every splat is updated by exactly one rank, so the replicated parameters stay
 // bit-identical on all ranks.
+// the same through L2 only (ld.global.cg): what a remote line needs - it lives in its home GPU's L2 - without the
+// system-scope ordering of ld.volatile (probe 16: is the strong load what makes the kernel slow?)
+__device__ __forceinline__ float4 ld_cg4( const float* p ) { return __ldcg( reinterpret_cast<const float4*>( p ) ); }
 __device__ __forceinline__ unsigned ld_sys_u32( const unsigned* p )
 {
 	unsigned v;
@@ -283,13 +286,13 @@ __device__ __forceinline__ unsigned reach_mask( float py, float sx, float sy, in
 }
 
 template <int NR>
-__global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, float* __restrict__ adam_m,
+__global__ void __launch_bounds__( 256 ) k_adam_peer( Geometry g, PeerPtrs pp, float* __restrict__ adam_m,
                                                       float* __restrict__ adam_v, gs2d_params hp,
                                                       const double* __restrict__ loss, DevState* st, int q0, int q1 )
 {
 	if( loss[g.n_images] != 0.0 || st->frozen )
 		return;
-	const int q = q0 + blockIdx.x * 128 + threadIdx.x;
+	const int q = q0 + blockIdx.x * blockDim.x + threadIdx.x;
 	if( q >= q1 )
 		return;
 	const int i4 = q * 4;
@@ -342,8 +345,9 @@ __global__ void __launch_bounds__( 128 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 			float4 part[NR];
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
-				part[r] = ( ( ( tmask >> r ) & 1u ) && !( ( pp.probe & 1 ) && r != pp.rank ) ) ? ld_sys4( pp.grads[r] + o )
-				                                                                              : make_float4( 0.f, 0.f, 0.f, 0.f ); // in flight together
+				part[r] = ( ( ( tmask >> r ) & 1u ) && !( ( pp.probe & 1 ) && r != pp.rank ) )
+				              ? ( ( pp.probe & 16 ) ? ld_cg4( pp.grads[r] + o ) : ld_sys4( pp.grads[r] + o ) )
+				              : make_float4( 0.f, 0.f, 0.f, 0.f ); // in flight together
 #pragma unroll
 			for( int r = 0; r < NR; r++ )
 			{
@@ -574,12 +578,13 @@ int launch_adam_peer( const Geometry& g, const Buffers& b, const gs2d_params& p,
 {
 	if( q1 <= q0 )
 		return 0;
-	const dim3 grid( ( q1 - q0 + 127 ) / 128, GS2D_NPLANES );
+	const int bs = ( pp.probe & 32 ) ? 256 : 128;
+	const dim3 grid( ( q1 - q0 + bs - 1 ) / bs, GS2D_NPLANES );
 #define PEER_CASE( NR )                                                                                               \
-	case NR: k_adam_peer<NR><<<grid, 128, 0, s>>>( g, pp, b.adam_m, b.adam_v, p, b.loss, b.state, q0, q1 ); break;
+	case NR: k_adam_peer<NR><<<grid, bs, 0, s>>>( g, pp, b.adam_m, b.adam_v, p, b.loss, b.state, q0, q1 ); break;
 	switch( pp.n_ranks )
 	{
-		PEER_CASE( 2 ) PEER_CASE( 3 ) PEER_CASE( 4 ) PEER_CASE( 5 ) PEER_CASE( 6 ) PEER_CASE( 7 ) PEER_CASE( 8 )
+		PEER_CASE( 1 ) PEER_CASE( 2 ) PEER_CASE( 3 ) PEER_CASE( 4 ) PEER_CASE( 5 ) PEER_CASE( 6 ) PEER_CASE( 7 ) PEER_CASE( 8 )
 	default: return 0;
 	}
 #undef PEER_CASE

@@ -174,6 +174,7 @@ struct gs2d_ctx
 	// peer-memory update (setup_peer_update): the other ranks' gradient / parameter / moment planes mapped through
 	// CUDA IPC; this rank owns the quads [own_q0, own_q1) of every plane (Adam moments are valid only there)
 	bool peer_update = false;
+	bool self_peer = false; // developer knob GS2D_PEER_SELF=1: the peer-memory update with ONE rank (profiling under ncu)
 	PeerPtrs peers{};
 	float* peer_m[GS2D_MAX_RANKS] = {};
 	float* peer_v[GS2D_MAX_RANKS] = {};
@@ -988,7 +989,8 @@ static int enqueue_allreduce( gs2d_ctx* c )
 static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_reduced )
 {
 	cudaStream_t s = c->stream;
-	const bool dbg = c->comm && c->peer_update && gs2d_tune( "GS2D_PEER_DEBUG", 0 ) && c->dbg_ev.size() < 5 * 4096;
+	const bool peer_path = ( c->comm || c->self_peer ) && c->peer_update;
+	const bool dbg = peer_path && gs2d_tune( "GS2D_PEER_DEBUG", 0 ) && c->dbg_ev.size() < 5 * 4096;
 	auto mark = [&]() {
 		if( dbg )
 		{
@@ -998,7 +1000,7 @@ static int enqueue_update( gs2d_ctx* c, cudaEvent_t ev_mid, bool grads_already_r
 			c->dbg_ev.push_back( e );
 		}
 	};
-	if( c->comm && c->peer_update )
+	if( peer_path )
 	{
 		mark();
 		int e = 0;
@@ -1731,7 +1733,53 @@ extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t
 	if( rc )
 		return rc;
 	if( n_ranks == 1 )
+	{
+		if( gs2d_tune( "GS2D_PEER_SELF", 0 ) )
+		{
+			// developer knob: run the peer-memory update path with this rank as its only peer, so that its kernels can be
+			// profiled on one GPU (ncu cannot replay a kernel that waits for another process)
+			if( !c->mbox )
+			{
+				CK( cudaMalloc( &c->mbox, peer_mailbox_bytes( c->g.n_images ) ) );
+				CK( cudaMemset( c->mbox, 0, peer_mailbox_bytes( c->g.n_images ) ) );
+				CK( cudaMalloc( &c->peer_seq, 2 * sizeof( unsigned long long ) ) );
+				CK( cudaMemset( c->peer_seq, 0, 2 * sizeof( unsigned long long ) ) );
+				const size_t touch_bytes = sizeof( unsigned ) * ( (size_t)c->g.n_pad / 128 + 1 ), nq = (size_t)c->g.n_pad / 4;
+				CK( cudaMalloc( &c->touch_mem, touch_bytes ) );
+				CK( cudaMemset( c->touch_mem, 0, touch_bytes ) );
+				CK( cudaMalloc( &c->reach_prev, 2 * nq ) );
+				CK( cudaMemset( c->reach_prev, 0xff, 2 * nq ) );
+				CK( cudaMalloc( &c->peer_traffic, 2 * sizeof( unsigned long long ) ) );
+				CK( cudaMemset( c->peer_traffic, 0, 2 * sizeof( unsigned long long ) ) );
+			}
+			PeerPtrs pp{};
+			pp.n_ranks = 1;
+			pp.rank = 0;
+			pp.sum_all = 1;
+			pp.grads[0] = c->b.grads;
+			pp.params[0] = c->b.params;
+			pp.mbox[0] = c->mbox;
+			pp.touch[0] = c->touch_mem;
+			pp.sparse = gs2d_tune( "GS2D_PEER_SPARSE", 1 ) ? 1 : 0;
+			pp.probe = gs2d_tune( "GS2D_PEER_PROBE", 0 );
+			pp.reach_prev = c->reach_prev;
+			pp.traffic = c->peer_traffic;
+			pp.band_tile_rows = c->g.tiles_y;
+			c->peer_m[0] = c->b.adam_m;
+			c->peer_v[0] = c->b.adam_v;
+			c->b.touch = pp.sparse ? c->touch_mem : nullptr;
+			c->peers = pp;
+			// GS2D_PEER_SELF=k > 1: own only 1/k of the quads, like one rank of k (the update of the others is skipped)
+			const int k = std::max( 1, gs2d_tune( "GS2D_PEER_SELF", 0 ) );
+			const int n4 = c->g.n_pad / 4;
+			c->own_q0 = 0;
+			c->own_q1 = ( n4 + k - 1 ) / k;
+			c->peer_update = true;
+			c->self_peer = true;
+			c->peer_flags = true;
+		}
 		return GS2D_OK;
+	}
 	ncclUniqueId_ u;
 	memcpy( u.internal, id, 128 );
 	int e = g_nccl.CommInitRank( &c->comm, n_ranks, u, rank );
