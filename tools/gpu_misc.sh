@@ -1,4 +1,5 @@
 #!/bin/bash
 OUT=gpurun_out; mkdir -p $OUT
-for k in 1 2 8; do GS2D_PEER_SELF=$k GS2D_PEER_DEBUG=1 python tools/peer_self.py 2>&1 | tail -2; done
-GS2D_PEER_SELF=8 QM_ITERS=3 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_adam_peer' -s 3 -c 1 -f -o $OUT/peer_self python tools/peer_self.py > $OUT/peer_self_ncu.log 2>&1; echo "ncu exit $?"
+timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider > $OUT/qi_pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/qi_pytest.log
+GS2D_STATS=0 timeout 300 python tools/quick_time.py 4096 1000000 30 2>&1 | tail -1 | cut -c40-200
+for k in 1 8; do GS2D_PEER_SELF=$k GS2D_PEER_DEBUG=1 python tools/peer_self.py 2>&1 | tail -1; done
