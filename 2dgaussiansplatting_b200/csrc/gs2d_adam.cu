@@ -268,23 +268,6 @@ __device__ __forceinline__ unsigned ld_sys_u32( const unsigned* p )
 	asm volatile( "ld.volatile.global.u32 %0, [%1];" : "=r"( v ) : "l"( p ) );
 	return v;
 }
-// bit r: a Gaussian with centre row py and scales sx, sy can reach the band of rank r (tile rows [r * per, (r+1) * per)).
-// The receiver's own test (k_preprocess: py +- (3 max(|sx|, |sy|) * 1.001 + 2)) is applied to the parameters AFTER this
-// iteration's Adam step, this one to those before it: one step moves py and the scales by lr each (the first Adam step
-// of a parameter is +-lr, later ones smaller), so 1 px more on each side makes it a superset. NaN reaches everyone,
-// like there.
-__device__ __forceinline__ unsigned reach_mask( float py, float sx, float sy, int per_rows_px, int n_ranks, float slack )
-{
-	const float h = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f + slack;
-	unsigned m = 0;
-	for( int r = 0; r < n_ranks; r++ )
-	{
-		const bool off = py + h < (float)( r * per_rows_px ) || py - h > (float)( ( r + 1 ) * per_rows_px );
-		m |= off ? 0u : ( 1u << r );
-	}
-	return m;
-}
-
 template <int NR>
 __global__ void __launch_bounds__( 256 ) k_adam_peer( Geometry g, PeerPtrs pp, float* __restrict__ adam_m,
                                                       float* __restrict__ adam_v, gs2d_params hp,
@@ -311,15 +294,12 @@ __global__ void __launch_bounds__( 256 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 		m = __ldcs( reinterpret_cast<const float4*>( adam_m + o ) );
 		v = __ldcs( reinterpret_cast<const float4*>( adam_v + o ) );
 	}
-	float4 rpy = m, rsx = m, rsy = m;
-	unsigned reach_last = 0;
+	unsigned reach_last = 0, reach_cur = 0;
 	const int par = st->iteration & 1; // k_advance has run: the parity of the iteration being finished
 	const size_t nq = (size_t)g.n_pad / 4;
 	if( pp.sparse )
 	{
-		rpy = *reinterpret_cast<const float4*>( own + (size_t)PL_PY * g.n_pad + i4 );
-		rsx = *reinterpret_cast<const float4*>( own + (size_t)PL_SX * g.n_pad + i4 );
-		rsy = *reinterpret_cast<const float4*>( own + (size_t)PL_SY * g.n_pad + i4 );
+		reach_cur = pp.reach_now[q];
 		reach_last = pp.reach_prev[(size_t)par * nq + q];
 	}
 	const float om_b1t = xsub( 1.0f, st->beta1t ), om_b2t = xsub( 1.0f, st->beta2t );
@@ -402,15 +382,9 @@ __global__ void __launch_bounds__( 256 ) k_adam_peer( Geometry g, PeerPtrs pp, f
 	unsigned send = ( 1u << NR ) - 1u;
 	if( pp.sparse )
 	{
-		// rpy / rsx / rsy may be the values before or after this very kernel's update of the three planes (their
-		// threads run concurrently): the slack covers one Adam step either way
-		const int per_px = pp.band_tile_rows * GS2D_TILE;
-		const float slack = 1.0f + 3.0f * hp.lr * 1.001f + hp.lr;
-		const unsigned now = reach_mask( rpy.x, rsx.x, rsy.x, per_px, NR, slack ) | reach_mask( rpy.y, rsx.y, rsy.y, per_px, NR, slack ) |
-		                     reach_mask( rpy.z, rsx.z, rsy.z, per_px, NR, slack ) | reach_mask( rpy.w, rsx.w, rsy.w, per_px, NR, slack );
-		send = now | reach_last | ( 1u << pp.rank );
+		send = reach_cur | reach_last | ( 1u << pp.rank );
 		if( pl == 0 )
-			pp.reach_prev[(size_t)( par ^ 1 ) * nq + q] = (unsigned char)now;
+			pp.reach_prev[(size_t)( par ^ 1 ) * nq + q] = (unsigned char)reach_cur;
 	}
 	if( changed )
 	{

@@ -184,6 +184,7 @@ struct gs2d_ctx
 	unsigned long long* peer_seq = nullptr; // device: [2] sequence numbers of barrier 1 / barrier 2, bumped by the kernels
 	unsigned* touch_mem = nullptr;          // device: this rank's touch bitmap (Buffers::touch points here while the sparse exchange is on)
 	unsigned char* reach_prev = nullptr;    // device: PeerPtrs::reach_prev
+	unsigned char* reach_now = nullptr;     // device: PeerPtrs::reach_now
 	unsigned long long* peer_traffic = nullptr; // device: PeerPtrs::traffic
 	long long traffic_iter0 = 0;            // expected_iteration when the traffic counters were last reset
 	bool peer_flags = true;                 // barriers over the mailboxes (else tiny NCCL all-reduces): GS2D_PEER_FLAGS
@@ -380,7 +381,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	                 b.rowrec,     b.rowtab,     b.target8,    b.u8_lut,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
-	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->peer_traffic };
+	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->reach_now, c->peer_traffic };
 	for( void* p : ptrs )
 		if( p )
 			cudaFree( p );
@@ -1604,6 +1605,8 @@ static int setup_peer_update( gs2d_ctx* c )
 		CK( cudaMemset( c->touch_mem, 0, touch_bytes ) );
 		CK( cudaMalloc( &c->reach_prev, 2 * nq ) );
 		CK( cudaMemset( c->reach_prev, 0xff, 2 * nq ) );
+		CK( cudaMalloc( &c->reach_now, nq ) );
+		CK( cudaMemset( c->reach_now, 0xff, nq ) );
 		CK( cudaMalloc( &c->peer_traffic, 2 * sizeof( unsigned long long ) ) );
 		CK( cudaMemset( c->peer_traffic, 0, 2 * sizeof( unsigned long long ) ) );
 	}
@@ -1655,6 +1658,7 @@ static int setup_peer_update( gs2d_ctx* c )
 	pp.sparse = gs2d_tune( "GS2D_PEER_SPARSE", 1 ) ? 1 : 0;
 	pp.probe = gs2d_tune( "GS2D_PEER_PROBE", 0 );
 	pp.reach_prev = c->reach_prev;
+	pp.reach_now = c->reach_now;
 	pp.traffic = gs2d_tune( "GS2D_PEER_TRAFFIC", 1 ) ? c->peer_traffic : nullptr;
 	pp.band_tile_rows = ( c->g.tiles_y + n - 1 ) / n; // set_band
 	// agree: the peer path is used only if every rank mapped every peer
@@ -1676,6 +1680,16 @@ static int setup_peer_update( gs2d_ctx* c )
 		c->peers = pp;
 		owned_quads( c, c->rank, &c->own_q0, &c->own_q1 );
 		c->peer_update = true;
+		if( pp.sparse )
+		{
+			// k_preprocess computes the reach masks of the quads this rank owns (PeerPtrs::reach_now)
+			c->b.reach.now = c->reach_now;
+			c->b.reach.q0 = c->own_q0;
+			c->b.reach.q1 = c->own_q1;
+			c->b.reach.n_ranks = n;
+			c->b.reach.band_px = pp.band_tile_rows * GS2D_TILE;
+			c->b.reach.slack = 1.0f + 3.0f * c->hp.lr * 1.001f + c->hp.lr;
+		}
 	}
 	else
 	{
@@ -1749,6 +1763,8 @@ extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t
 				CK( cudaMemset( c->touch_mem, 0, touch_bytes ) );
 				CK( cudaMalloc( &c->reach_prev, 2 * nq ) );
 				CK( cudaMemset( c->reach_prev, 0xff, 2 * nq ) );
+				CK( cudaMalloc( &c->reach_now, nq ) );
+				CK( cudaMemset( c->reach_now, 0xff, nq ) );
 				CK( cudaMalloc( &c->peer_traffic, 2 * sizeof( unsigned long long ) ) );
 				CK( cudaMemset( c->peer_traffic, 0, 2 * sizeof( unsigned long long ) ) );
 			}
@@ -1763,6 +1779,7 @@ extern "C" int gs2d_comm_init( gs2d_ctx* c, int rank, int n_ranks, const uint8_t
 			pp.sparse = gs2d_tune( "GS2D_PEER_SPARSE", 1 ) ? 1 : 0;
 			pp.probe = gs2d_tune( "GS2D_PEER_PROBE", 0 );
 			pp.reach_prev = c->reach_prev;
+			pp.reach_now = c->reach_now; // stays 0xff: everything reaches the only rank
 			pp.traffic = c->peer_traffic;
 			pp.band_tile_rows = c->g.tiles_y;
 			c->peer_m[0] = c->b.adam_m;

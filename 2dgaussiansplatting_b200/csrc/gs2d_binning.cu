@@ -93,7 +93,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
                                                                SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
                                                                PairOut out, unsigned long long capacity, int cull,
                                                                int relaxed, int rowtab, unsigned* __restrict__ touch,
-                                                               DevState* __restrict__ st )
+                                                               Buffers::Reach reach, DevState* __restrict__ st )
 {
 	const int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -108,6 +108,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 	sb.k.begY = 1;
 	sb.k.endY = 0;
 	bool in_band = false; // passed the band test: the only splats that can receive a gradient on this rank
+	unsigned reaches = 0; // sparse exchange: the ranks this splat can reach (computed for the quads this rank owns)
 	if( gi < g.n_total )
 	{
 		const float px = params[PL_PX * g.n_pad + gi];
@@ -115,6 +116,8 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 		const float sx = params[PL_SX * g.n_pad + gi];
 		const float sy = params[PL_SY * g.n_pad + gi];
 		const float rot = params[PL_ROT * g.n_pad + gi];
+		if( reach.now && ( gi >> 2 ) >= reach.q0 && ( gi >> 2 ) < reach.q1 )
+			reaches = reach_mask( py, sx, sy, reach.band_px, reach.n_ranks, reach.slack );
 
 		// A rank that owns a band of tile rows skips the splats that cannot reach it before any of the expensive
 		// work (double sincos, five IEEE divisions, the 64-byte record, which only this rank's blend would read):
@@ -229,6 +232,16 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 			sb.k.begY = begY;
 			sb.k.endY = endY;
 		}
+	}
+	if( reach.now )
+	{
+		// OR over the four splats of the quad; the first lane of the quad stores the byte
+		unsigned m = reaches;
+		m |= __shfl_xor_sync( 0xffffffffu, m, 1 );
+		m |= __shfl_xor_sync( 0xffffffffu, m, 2 );
+		const int q = gi >> 2;
+		if( ( lane & 3 ) == 0 && q >= reach.q0 && q < reach.q1 )
+			reach.now[q] = (unsigned char)m;
 	}
 	if( touch )
 	{
@@ -653,10 +666,10 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
 	if( slots )
 		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                               relaxed, rowtab, b.touch, b.state );
+		                                               relaxed, rowtab, b.touch, b.reach, b.state );
 	else
 		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                                relaxed, rowtab, b.touch, b.state );
+		                                                relaxed, rowtab, b.touch, b.reach, b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );

@@ -166,6 +166,14 @@ struct Buffers
 	double* loss_partial;     // [n_tiles_total]
 	unsigned* tile_done;      // [n_tiles_total] forward -> backward tile flags of the PDL overlap (gs2d_blend.cuh)
 	unsigned* touch;          // [n_pad / 128 + 1] bitmap of the quads that passed this rank's band test (PeerPtrs::touch); nullptr on one GPU
+	// sparse parameter broadcast (PeerPtrs::reach_now): k_preprocess computes, for the quads this rank OWNS
+	// [reach_q0, reach_q1), the mask of the ranks whose band a Gaussian of the quad can reach
+	struct Reach
+	{
+		unsigned char* now; // [n_pad / 4]; nullptr: not needed
+		int q0, q1, n_ranks, band_px;
+		float slack;
+	} reach;
 	unsigned long long* live_slots;   // [GS2D_LIVE_SLOTS]
 	unsigned long long* staged_slots; // [GS2D_LIVE_SLOTS], contiguous after live_slots
 	unsigned long long* stats;        // [2] live pairs, staged entries of the last forward (summed slots)
@@ -178,6 +186,21 @@ struct Buffers
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
 int launch_u8_lut( float* lut, cudaStream_t s );
+// bit r: a Gaussian with centre row py and scales sx, sy can reach the band of rank r (pixel rows [r * band_px,
+// (r+1) * band_px)). The receiver's own test (k_preprocess: py +- (3 max(|sx|, |sy|) * 1.001 + 2)) is applied to the
+// parameters AFTER this iteration's Adam step, this one to those before it: one step moves py and the scales by at
+// most lr each, so `slack` = 1 px + 3 lr + lr more on each side makes it a superset. NaN reaches everyone, like there.
+__device__ __forceinline__ unsigned reach_mask( float py, float sx, float sy, int band_px, int n_ranks, float slack )
+{
+	const float h = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f + slack;
+	unsigned m = 0;
+	for( int r = 0; r < n_ranks; r++ )
+	{
+		const bool off = py + h < (float)( r * band_px ) || py - h > (float)( ( r + 1 ) * band_px );
+		m |= off ? 0u : ( 1u << r );
+	}
+	return m;
+}
 // the reference pixel of the loss / of dL/dC (imageRef, main.cpp:616, :800) in either target format
 __device__ __forceinline__ float4 load_target( const Geometry& g, const float4* __restrict__ target, size_t pix )
 {
@@ -238,6 +261,8 @@ struct PeerPtrs
 	//              its kernels look at; gs2d_download_state gathers the rest from the owners.
 	const unsigned* touch[GS2D_MAX_RANKS];
 	unsigned char* reach_prev; // [2][n_pad / 4] double-buffered by iteration parity: ranks reached at the last exchange
+	const unsigned char* reach_now; // [n_pad / 4] ranks a quad's Gaussians reach, computed by k_preprocess of this iteration
+	                           // (from the parameters BEFORE the Adam step; the slack of the test covers the step)
 	unsigned long long* traffic; // [2] 16-byte quads read from / written to peers over NVLink (running sums)
 	int sparse;
 	int band_tile_rows;        // tile rows per rank (set_band)
