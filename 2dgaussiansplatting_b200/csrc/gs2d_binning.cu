@@ -119,12 +119,9 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 		if( reach.now && ( gi >> 2 ) >= reach.q0 && ( gi >> 2 ) < reach.q1 )
 			reaches = reach_mask( py, sx, sy, reach.band_px, reach.n_ranks, reach.slack );
 
-		// A rank that owns a band of tile rows skips the splats that cannot reach it before any of the expensive
-		// work (double sincos, five IEEE divisions, the 64-byte record, which only this rank's blend would read):
-		// cov[1][1] <= max(sx, sy)^2 whatever the rotation, so the reference's rows lie within py +- 3 max(sx, sy);
-		// 2 px and 1e-3 relative cover the truncation and the float error of the exact bound. NaNs fall through.
-		const float hmax = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f;
-		const bool off_band = py + hmax < (float)( g.band_ty0 * GS2D_TILE ) || py - hmax > (float)( g.band_ty1 * GS2D_TILE );
+		// a rank that owns a band of tile rows skips the splats that cannot reach it (band_rejects, gs2d_footprint.cuh)
+		// before the double sincos, the five IEEE divisions and the records, which only this rank's blend would read
+		const bool off_band = band_rejects( py, sx, sy, g.band_ty0 * GS2D_TILE, g.band_ty1 * GS2D_TILE );
 		in_band = !off_band;
 		if( off_band )
 			rowrec[gi].rows = ROWREC_NONE; // k_row_table looks at every splat

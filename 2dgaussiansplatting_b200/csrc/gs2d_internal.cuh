@@ -186,21 +186,6 @@ struct Buffers
 int launch_init_reference( const Geometry& g, const Buffers& b, cudaStream_t s );
 int launch_u8_to_target( const uint8_t* src_dev, float4* dst, size_t n_px, cudaStream_t s );
 int launch_u8_lut( float* lut, cudaStream_t s );
-// bit r: a Gaussian with centre row py and scales sx, sy can reach the band of rank r (pixel rows [r * band_px,
-// (r+1) * band_px)). The receiver's own test (k_preprocess: py +- (3 max(|sx|, |sy|) * 1.001 + 2)) is applied to the
-// parameters AFTER this iteration's Adam step, this one to those before it: one step moves py and the scales by at
-// most lr each, so `slack` = 1 px + 3 lr + lr more on each side makes it a superset. NaN reaches everyone, like there.
-__device__ __forceinline__ unsigned reach_mask( float py, float sx, float sy, int band_px, int n_ranks, float slack )
-{
-	const float h = 3.0f * fmaxf( fabsf( sx ), fabsf( sy ) ) * 1.001f + 2.0f + slack;
-	unsigned m = 0;
-	for( int r = 0; r < n_ranks; r++ )
-	{
-		const bool off = py + h < (float)( r * band_px ) || py - h > (float)( ( r + 1 ) * band_px );
-		m |= off ? 0u : ( 1u << r );
-	}
-	return m;
-}
 // the reference pixel of the loss / of dL/dC (imageRef, main.cpp:616, :800) in either target format
 __device__ __forceinline__ float4 load_target( const Geometry& g, const float4* __restrict__ target, size_t pix )
 {

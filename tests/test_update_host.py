@@ -111,3 +111,58 @@ def test_nonfinite_gradients_are_flagged_like_the_reference_aborts(up):
             # pos.y and (unoptimised) opacity are not part of the reference's finite check (main.cpp:752-785)
             if (name, sub) in (("pos", 1), ("opacity", None)):
                 assert bad == 0
+
+
+@pytest.mark.parametrize("n_ranks,H,lr", [(8, 4096, 0.05), (2, 520, 0.05), (4, 1024, 2.0)])
+def test_sparse_parameter_broadcast_keeps_every_rank_exact_where_it_looks(up, n_ranks, H, lr):
+    """The sparse exchange of the multi-GPU path, simulated on the CPU with the product's own two band
+    tests (band_rejects = what k_preprocess of a rank applies, reach_mask = what the owner applies; gs2d_footprint.cuh
+    compiled for the host): the owner sends a Gaussian's new parameters to the ranks in reach_now | reach_prev only.
+    Invariant, at EVERY iteration and for EVERY rank: the rank's own copy equals the true parameters for every
+    Gaussian its band test does not reject. Gaussians random-walk across the band boundaries with Adam-sized steps
+    (|d py|, |d sx|, |d sy| <= lr per iteration), some in big jumps at the start of 'uploads' (all copies refreshed)."""
+    up.up_band_tests.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p,
+                                 C.c_void_p]
+    rng = np.random.default_rng(n_ranks)
+    n = 6000
+    tiles_y = (H + 15) // 16
+    band_px = ((tiles_y + n_ranks - 1) // n_ranks) * 16
+    slack = np.float32(1.0 + 3.0 * lr * 1.001 + lr)  # gs2d_api.cu, setup_peer_update
+
+    def tests(p):
+        rej = np.zeros((n_ranks, n), np.uint8)
+        masks = np.zeros(n, np.uint32)
+        up.up_band_tests(n, _p(p[0]), _p(p[1]), _p(p[2]), band_px, n_ranks, slack, _p(rej), _p(masks))
+        return rej.astype(bool), masks
+
+    true = np.stack([rng.uniform(-20, H + 20, n), rng.uniform(1, 40, n), rng.uniform(1, 40, n)]).astype(np.float32)
+    true[1, ::50] = 1024.0  # a few that reach every band
+    true[0, 7] = np.nan     # NaN reaches everyone and is never rejected
+    copies = [true.copy() for _ in range(n_ranks)]
+    prev = np.full(n, (1 << n_ranks) - 1, np.uint32)  # after an upload: everything is sent once
+    stale_seen = 0
+    for it in range(300):
+        _, now = tests(true)                           # k_preprocess of the owner, parameters BEFORE the step
+        step = rng.uniform(-lr, lr, true.shape).astype(np.float32)
+        step[:, rng.random(n) < 0.3] = 0               # occluded Gaussians do not move
+        new = true + step
+        new[1:] = np.clip(new[1:], 1.0, 1024.0)        # main.cpp:744-745
+        send = now | prev
+        for r in range(n_ranks):
+            sel = (send >> r) & 1 == 1
+            copies[r][:, sel] = new[:, sel]
+        prev, true = now, new
+        rej, _ = tests(true)                           # k_preprocess of every rank at the NEXT iteration
+        for r in range(n_ranks):
+            look = ~rej[r]
+            same = (copies[r].view(np.uint32) == true.view(np.uint32)).all(axis=0)
+            assert same[look].all(), (it, r, np.flatnonzero(look & ~same)[:5])
+            # ... and a rank that does not look must also reject its STALE copy (else it would blend stale data)
+            rej_stale = np.zeros((n_ranks, n), np.uint8)
+            m2 = np.zeros(n, np.uint32)
+            c = copies[r]
+            up.up_band_tests(n, _p(np.ascontiguousarray(c[0])), _p(np.ascontiguousarray(c[1])), _p(np.ascontiguousarray(c[2])),
+                             band_px, n_ranks, slack, _p(rej_stale), _p(m2))
+            assert (rej_stale[r].astype(bool) | same).all(), (it, r)
+            stale_seen += int((~same).sum())
+    assert stale_seen > 0  # the test did exercise stale copies

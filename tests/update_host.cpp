@@ -53,4 +53,18 @@ int up_adam( int W, int H, int n, float* splats, float* adam, const float* grads
 		}
 	return bad;
 }
+
+// The two band tests of the multi-GPU partition (gs2d_footprint.cuh), for the simulation of the sparse parameter
+// broadcast in tests/test_update_host.py. n splats; rejects[r * n + i] = band_rejects on rank r's band
+// [r * band_px, (r+1) * band_px); masks[i] = reach_mask.
+void up_band_tests( int n, const float* py, const float* sx, const float* sy, int band_px, int n_ranks, float slack,
+                    uint8_t* rejects, uint32_t* masks )
+{
+	for( int i = 0; i < n; i++ )
+	{
+		for( int r = 0; r < n_ranks; r++ )
+			rejects[(size_t)r * n + i] = band_rejects( py[i], sx[i], sy[i], r * band_px, ( r + 1 ) * band_px ) ? 1 : 0;
+		masks[i] = reach_mask( py[i], sx[i], sy[i], band_px, n_ranks, slack );
+	}
+}
 }
