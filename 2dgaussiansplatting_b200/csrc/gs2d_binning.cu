@@ -562,6 +562,11 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 	if( i >= n_buckets )
 		return;
 	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
+	// all four loads of a bucket (counter, offset, block sum, slot row) are independent: requested together, one
+	// memory round trip instead of two (the kernel waits on L2, profiles/r2_ncu.txt: 9 long-scoreboard stalls per issue)
+	uint4 w = make_uint4( 0u, 0u, 0u, 0u );
+	if( SLOTS )
+		w = __ldcs( reinterpret_cast<const uint4*>( slots + ( (size_t)slice * g.nt_pad + tile ) * GS2D_BUCKET_SLOTS ) );
 	const unsigned n = cnt16[(size_t)slice * g.nt_pad + tile];
 	const unsigned start = bucket_offset( offset, sums, i, base );
 	if( slice == 0 )
@@ -576,7 +581,6 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		static_assert( GS2D_BUCKET_SLOTS == 8, "k_rank reads a slot row as one uint4 and sorts 8 registers" );
 		if( n == 0u )
 			return;
-		const uint4 w = __ldcs( reinterpret_cast<const uint4*>( slots + ( (size_t)slice * g.nt_pad + tile ) * GS2D_BUCKET_SLOTS ) );
 		// all entries of a bucket share the image and the slice: global index = first + index inside the slice
 		const unsigned first = ( tile / (unsigned)( g.tiles_x * g.tiles_y ) ) * (unsigned)g.n_splats + slice * (unsigned)g.slice_size;
 		sl[0] = first + ( w.x & 0xffffu );
