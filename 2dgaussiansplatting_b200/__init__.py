@@ -36,6 +36,7 @@ ADAM_DTYPE = np.dtype(
 )
 
 GS2D_OK = 0
+GS2D_ERR_INVALID = -1
 GS2D_ERR_NONFINITE = -4
 
 # every symbol include/gs2d.h declares (tests check the library exports all of them)
@@ -49,7 +50,7 @@ ABI_SYMBOLS = [
     "gs2d_microbench_fp32", "gs2d_microbench_hbm",
     "gs2d_get_optimize_opacity", "gs2d_get_dims", "gs2d_set_target_rgba8_async", "gs2d_comm_mode", "gs2d_comm_traffic", "gs2d_save_checkpoint", "gs2d_load_checkpoint",
     "gs2d_image_load_rgba8", "gs2d_image_decode_jpeg_rgba8", "gs2d_image_free", "gs2d_image_write_ppm",
-    "gs2d_overlay_geometry",
+    "gs2d_overlay_geometry", "gs2d_mse_static",
 ]
 
 
@@ -127,6 +128,7 @@ def load_library():
     L.gs2d_sync.argtypes = [vp]
     L.gs2d_microbench_fp32.argtypes = [i, C.POINTER(C.c_double)]
     L.gs2d_microbench_hbm.argtypes = [i, C.POINTER(C.c_double)]
+    L.gs2d_mse_static.argtypes = [i, vp, vp, i, i, vp, vp, C.c_char_p, C.c_size_t]
     L.gs2d_get_optimize_opacity.argtypes = [vp, C.POINTER(i)]
     L.gs2d_get_dims.argtypes = [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)]
     L.gs2d_save_checkpoint.argtypes = [vp, C.c_char_p]
@@ -492,3 +494,18 @@ def microbench(device=0):
     if rc != GS2D_OK:
         raise Gs2dError(rc, L.gs2d_strerror(rc).decode())
     return t.value, g.value
+
+
+def mse_static(image_ptr, target_ptr, W, H, mse_ptr, stream=None, device=0):
+    """gs2d_mse_static: the loss of main.cpp:796-805 over DEVICE buffers of the caller, allocating nothing (scratch in a
+    static __device__ array of the library, GS2D_MSE_STATIC_MAX_TILES tiles). Arguments are raw device addresses; the
+    result lands in *mse_ptr when the stream reaches it. No counterpart in the reference."""
+    L = load_library()
+    err = C.create_string_buffer(256)
+    rc = L.gs2d_mse_static(int(device), C.c_void_p(image_ptr), C.c_void_p(target_ptr), int(W), int(H),
+                           C.c_void_p(mse_ptr), C.c_void_p(stream or 0), err, len(err))
+    if rc != GS2D_OK:
+        raise Gs2dError(rc, err.value.decode() or L.gs2d_strerror(rc).decode())
+
+
+MSE_STATIC_MAX_TILES = 65536

@@ -243,6 +243,25 @@ int gs2d_overlay_geometry( const gs2d_splat* splats, int n, int nvtx, gs2d_overl
 int gs2d_microbench_fp32( int device, double* tflops );
 int gs2d_microbench_hbm( int device, double* gbs );
 
+/* The loss of main.cpp:796-805, mean over 3*W*H of (255*(image - target))^2, on DEVICE buffers the caller owns, without
+ * allocating anything. This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). It calls no cudaMalloc / cudaFree / allocating library routine and needs no gs2d_ctx.
+ *   image_dev, target_dev  row-major RGBA float32 (16-byte aligned) of W x H pixels on `device`; alpha is ignored
+ *   mse_dev                one double on `device`, written by the second of the two kernels enqueued on cuda_stream
+ *   cuda_stream            a cudaStream_t (NULL = the default stream); the call returns once both kernels are enqueued
+ *   err, err_cap           NULL/0, or a buffer that receives the text of a failure ("" on success)
+ * The per-tile partial sums live in a file-scope static __device__ array of GS2D_MSE_STATIC_MAX_TILES doubles
+ * (512 KiB, held by every GPU that loads the library until the process exits): images of more 16x16 tiles than that
+ * (e.g. beyond 4096 x 4096) are rejected with GS2D_ERR_INVALID. All calls on a device share the array: calls that
+ * overlap on the GPU (two streams) race - serialise them. Nothing in it has to be cleared between calls (each call
+ * overwrites exactly the range it then reads). The summation order is the one of gs2d_forward + gs2d_last_mse, so the
+ * value is the same bit for bit. The call makes `device` current; the first call per device looks the array's
+ * address up (cudaGetSymbolAddress) - make that one outside a stream capture. */
+#define GS2D_MSE_STATIC_MAX_TILES 65536
+int gs2d_mse_static( int device, const float* image_dev, const float* target_dev, int W, int H, double* mse_dev,
+                     void* cuda_stream, char* err, size_t err_cap );
+
 #ifdef __cplusplus
 }
 #endif
