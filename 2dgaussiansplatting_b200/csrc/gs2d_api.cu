@@ -133,6 +133,11 @@ struct gs2d_ctx
 	cudaEvent_t copy_done[2] = { nullptr, nullptr }, convert_done[2] = { nullptr, nullptr };
 	int ustage_next = 0;
 	int pending_buf = -1, pending_image = 0; // an uploaded target that has not been taken over yet
+	// One-image contexts read an asynchronously uploaded RGBA8 target where the copy engine put it: Buffers::target8
+	// points at staging buffer `adopted_buf` (no device-to-device copy on the compute stream); target8_own is the
+	// buffer the blocking uploads and image batches use. convert_done[k] then means "nothing enqueued reads buffer k".
+	uchar4* target8_own = nullptr;
+	int adopted_buf = -1;
 	std::vector<char> img_fmt;               // per image: 0 no target yet (zeros), 1 float32, 2 RGBA8 (target_store_u8)
 	size_t pending_px0 = 0, pending_npx = 0;
 
@@ -144,12 +149,20 @@ struct gs2d_ctx
 		Geometry g;
 		gs2d_params hp;
 		void* ptr[8];
+		void* target8;
 		unsigned long long capacity;
 		int mse_cap, count_live, tune_epoch, pad;
 	};
-	cudaGraphExec_t iter_graph = nullptr;
-	GraphKey graph_key{};
-	int graph_nodes = 0;
+	// two slots: a caller that streams targets alternates between the two staging buffers (GraphKey::target8)
+	struct GraphSlot
+	{
+		cudaGraphExec_t exec = nullptr;
+		GraphKey key{};
+		int nodes = 0;
+		uint64_t used = 0;
+	};
+	GraphSlot graphs[2];
+	uint64_t graph_clock = 0;
 
 	long long expected_iteration = 0; // what the device counter will read once everything enqueued has run
 
@@ -356,8 +369,9 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 		for( cudaEvent_t e : c->dbg_ev )
 			cudaEventDestroy( e );
 	}
-	if( c->iter_graph )
-		cudaGraphExecDestroy( c->iter_graph );
+	for( gs2d_ctx::GraphSlot& gs : c->graphs )
+		if( gs.exec )
+			cudaGraphExecDestroy( gs.exec );
 	for( auto& t : c->tickets )
 		if( t.ev )
 			cudaEventDestroy( t.ev );
@@ -378,7 +392,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->side.ev_join )
 		cudaEventDestroy( c->side.ev_join );
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
-	                 b.rowrec,     b.rowtab,     b.target8,    b.u8_lut,
+	                 b.rowrec,     b.rowtab,     c->target8_own, b.u8_lut,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->reach_now, c->peer_traffic };
@@ -581,6 +595,7 @@ static const void* h2d_source( gs2d_ctx* c, const void* user, size_t bytes )
 }
 
 static int apply_pending_target( gs2d_ctx* c );
+static int release_adopted( gs2d_ctx* c );
 
 extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgba )
 {
@@ -606,6 +621,9 @@ extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgb
 				c->img_fmt[(size_t)i] = 1;
 			}
 		c->g.target_u8 = 0;
+		rc = release_adopted( c );
+		if( rc )
+			return rc;
 	}
 	CK( cudaMemcpyAsync( c->b.target + (size_t)image * n_px, h2d_source( c, rgba, bytes ), bytes, cudaMemcpyHostToDevice,
 	                     c->stream ) );
@@ -618,7 +636,21 @@ extern "C" int gs2d_set_target_rgba32f( gs2d_ctx* c, int image, const float* rgb
 // As long as no image of the context has a float32 target, the 8-bit pixels are kept as they are and the blend kernels
 // convert on the fly (Geometry::target_u8): one device-to-device copy of 4 bytes per pixel instead of a conversion
 // pass that reads 4 and writes 16. Otherwise they are converted into the float32 target as before.
-static int target_store_u8( gs2d_ctx* c, int image, const uint8_t* dev_src, size_t px0, size_t npx )
+// adopt >= 0: dev_src is staging buffer `adopt`, holding the rows at their place in a whole-image buffer (ustage[adopt] +
+// px0): a one-image context then reads the target there instead of copying it (gs2d_ctx::adopted_buf).
+static int release_adopted( gs2d_ctx* c )
+{
+	if( c->adopted_buf >= 0 )
+	{
+		// everything enqueued so far may read the buffer; the copy stream waits for this before it overwrites it
+		CK( cudaEventRecord( c->convert_done[c->adopted_buf], c->stream ) );
+		c->adopted_buf = -1;
+	}
+	c->b.target8 = c->target8_own;
+	return GS2D_OK;
+}
+
+static int target_store_u8( gs2d_ctx* c, int image, const uint8_t* dev_src, size_t px0, size_t npx, int adopt = -1 )
 {
 	const size_t n_px = (size_t)c->g.W * c->g.H;
 	bool any_float = false;
@@ -631,12 +663,27 @@ static int target_store_u8( gs2d_ctx* c, int image, const uint8_t* dev_src, size
 		c->img_fmt[(size_t)image] = 1;
 		return check_launch( c );
 	}
-	if( !c->b.target8 )
+	if( adopt >= 0 && c->g.n_images == 1 && gs2d_tune( "GS2D_ADOPT_TARGET", 1 ) != 0 )
+	{
+		int rc = release_adopted( c ); // the buffer read so far is free once what has been enqueued has run
+		if( rc )
+			return rc;
+		c->adopted_buf = adopt;
+		c->b.target8 = reinterpret_cast<uchar4*>( c->ustage[adopt] );
+		c->img_fmt[(size_t)image] = 2;
+		c->g.target_u8 = 1;
+		return GS2D_OK;
+	}
+	int rc = release_adopted( c );
+	if( rc )
+		return rc;
+	if( !c->target8_own )
 	{
 		const size_t bytes = sizeof( uchar4 ) * n_px * (size_t)c->g.n_images;
-		CK( cudaMalloc( &c->b.target8, bytes ) );
-		CK( cudaMemsetAsync( c->b.target8, 0, bytes, c->stream ) ); // images without a target: zeros, as in the float32 buffer
+		CK( cudaMalloc( &c->target8_own, bytes ) );
+		CK( cudaMemsetAsync( c->target8_own, 0, bytes, c->stream ) ); // images without a target: zeros, as in the float32 buffer
 	}
+	c->b.target8 = c->target8_own;
 	if( npx )
 		CK( cudaMemcpyAsync( c->b.target8 + (size_t)image * n_px + px0, dev_src, npx * 4, cudaMemcpyDeviceToDevice, c->stream ) );
 	c->img_fmt[(size_t)image] = 2;
@@ -666,10 +713,11 @@ static int apply_pending_target( gs2d_ctx* c )
 	const int k = c->pending_buf;
 	c->pending_buf = -1;
 	CK( cudaStreamWaitEvent( c->stream, c->copy_done[k], 0 ) );
-	int rc = target_store_u8( c, c->pending_image, c->ustage[k], c->pending_px0, c->pending_npx );
+	int rc = target_store_u8( c, c->pending_image, c->ustage[k] + c->pending_px0 * 4, c->pending_px0, c->pending_npx, k );
 	if( rc )
 		return rc;
-	CK( cudaEventRecord( c->convert_done[k], c->stream ) );
+	if( c->adopted_buf != k ) // copied or converted: the staging buffer is free once that has run
+		CK( cudaEventRecord( c->convert_done[k], c->stream ) );
 	return check_launch( c );
 }
 
@@ -734,6 +782,7 @@ extern "C" int gs2d_set_target_rgba8_async( gs2d_ctx* c, int image, const uint8_
 				cudaFree( c->ustage[k] );
 			c->ustage[k] = nullptr;
 			CK( cudaMalloc( &c->ustage[k], full ) );
+			CK( cudaMemsetAsync( c->ustage[k], 0, full, c->stream ) ); // rows outside a band: zeros, like target8_own
 			CK( cudaEventRecord( c->convert_done[k], c->stream ) );
 		}
 		c->ustage_bytes = full;
@@ -743,7 +792,7 @@ extern "C" int gs2d_set_target_rgba8_async( gs2d_ctx* c, int image, const uint8_
 	// the buffer is free once the conversion that last read it has run
 	CK( cudaStreamWaitEvent( c->copy_stream, c->convert_done[k], 0 ) );
 	if( bytes )
-		CK( cudaMemcpyAsync( c->ustage[k], rgba + px0 * 4, bytes, cudaMemcpyHostToDevice, c->copy_stream ) );
+		CK( cudaMemcpyAsync( c->ustage[k] + px0 * 4, rgba + px0 * 4, bytes, cudaMemcpyHostToDevice, c->copy_stream ) );
 	CK( cudaEventRecord( c->copy_done[k], c->copy_stream ) );
 	c->pending_buf = k;
 	c->pending_image = image;
@@ -1123,43 +1172,54 @@ static int enqueue_iterations( gs2d_ctx* c, int n )
 		key.ptr[5] = c->b.bucket_cnt;
 		key.ptr[6] = c->comm;
 		key.ptr[7] = c->peer_update ? (void*)c->peers.mbox[c->rank] : nullptr;
+		key.target8 = c->b.target8;
 		key.capacity = c->b.capacity;
 		key.mse_cap = c->b.mse_cap;
 		key.count_live = c->count_live ? 1 : 0;
 		key.tune_epoch = g_tune_epoch;
 		key.pad = c->slot_binning ? 1 : 0;
-		if( !c->iter_graph || memcmp( &key, &c->graph_key, sizeof( key ) ) != 0 )
+		gs2d_ctx::GraphSlot* slot = nullptr;
+		for( gs2d_ctx::GraphSlot& gs : c->graphs )
+			if( gs.exec && memcmp( &key, &gs.key, sizeof( key ) ) == 0 )
+				slot = &gs;
+		if( !slot )
 		{
-			if( c->iter_graph )
-				cudaGraphExecDestroy( c->iter_graph );
-			c->iter_graph = nullptr;
+			// replace the slot used longest ago (or an empty one)
+			slot = &c->graphs[0];
+			for( gs2d_ctx::GraphSlot& gs : c->graphs )
+				if( !gs.exec || ( slot->exec && gs.used < slot->used ) )
+					slot = &gs;
+			if( slot->exec )
+				cudaGraphExecDestroy( slot->exec );
+			slot->exec = nullptr;
 			const uint64_t launches0 = c->launches;
 			const long long expected0 = c->expected_iteration;
 			cudaGraph_t graph = nullptr;
 			CK( cudaStreamBeginCapture( c->stream, cudaStreamCaptureModeThreadLocal ) );
 			rc = enqueue_iteration( c );
 			cudaError_t e = cudaStreamEndCapture( c->stream, &graph );
-			c->graph_nodes = (int)( c->launches - launches0 );
+			slot->nodes = (int)( c->launches - launches0 );
 			c->launches = launches0;
 			c->expected_iteration = expected0;
 			if( rc == GS2D_OK && e == cudaSuccess && graph )
-				e = cudaGraphInstantiate( &c->iter_graph, graph, 0 );
+				e = cudaGraphInstantiate( &slot->exec, graph, 0 );
 			if( graph )
 				cudaGraphDestroy( graph );
 			if( rc != GS2D_OK || e != cudaSuccess )
 			{
 				cudaGetLastError();
-				c->iter_graph = nullptr; // capture unavailable: plain launches below
+				slot->exec = nullptr; // capture unavailable: plain launches below
 			}
 			else
-				c->graph_key = key;
+				slot->key = key;
 		}
-		if( c->iter_graph )
+		if( slot->exec )
 		{
+			slot->used = ++c->graph_clock;
 			for( int i = 0; i < n; i++ )
 			{
-				CK( cudaGraphLaunch( c->iter_graph, c->stream ) );
-				c->launches += (uint64_t)c->graph_nodes;
+				CK( cudaGraphLaunch( slot->exec, c->stream ) );
+				c->launches += (uint64_t)slot->nodes;
 				c->expected_iteration++;
 			}
 			c->have_forward = false;

@@ -173,6 +173,55 @@ def test_async_target_upload_equals_blocking():
         assert np.allclose(a.step(1), b.step(1), rtol=1e-9)
 
 
+def test_streamed_targets_are_read_in_place():
+    """A one-image context reads an asynchronously uploaded target in the staging buffer the copy engine filled (no
+    device-to-device copy; two buffers, one cached graph each): a stream of different targets, one per iteration and
+    pipelined like bench.py's e2e loop, gives the losses of blocking uploads; a float32 target then takes over."""
+    import torch
+
+    W, H, N = 333, 270, 700
+    rng = np.random.default_rng(6)
+    t = [rng.integers(0, 256, (H, W, 4), dtype=np.uint8) for _ in range(3)]
+    pin = [torch.from_numpy(x.copy()).pin_memory() for x in t]
+    seq = [0, 1, 2, 1, 0, 2, 2, 1, 0]
+    with gs2d.Fitter(W, H, N) as a, gs2d.Fitter(W, H, N) as b:
+        a.set_target_u8(t[0])
+        a.restart()
+        b.set_target_u8_ptr_async(pin[0].data_ptr())
+        b.restart()
+        ma = []
+        for k in seq:
+            a.set_target_u8(t[k])
+            ma.append(a.step(1)[0, 0])
+        mb, prev = [], None
+        b.set_target_u8_ptr_async(pin[seq[0]].data_ptr())
+        for i in range(len(seq)):
+            b.step(1, want_mse=False)
+            ticket = b.mse_ticket()
+            if i + 1 < len(seq):
+                b.set_target_u8_ptr_async(pin[seq[i + 1]].data_ptr())  # lands while iteration i runs
+            if prev is not None:
+                mb.append(b.mse_wait(prev)[0])
+            prev = ticket
+        mb.append(b.mse_wait(prev)[0])
+        assert mb[0] == ma[0] and np.allclose(ma, mb, rtol=1e-7, atol=0), (ma, mb)
+        assert len(set(ma)) == len(ma)
+        # several iterations on one streamed target, then a blocking upload, then float32
+        b.set_target_u8_ptr_async(pin[2].data_ptr())
+        a.set_target_u8(t[2])
+        assert np.allclose(a.step(3), b.step(3), rtol=1e-8)
+        b.set_target_u8(t[1])
+        a.set_target_u8(t[1])
+        assert np.allclose(a.step(2), b.step(2), rtol=1e-8)
+        b.set_target_u8_ptr_async(pin[0].data_ptr())
+        a.set_target_u8(t[0])
+        assert np.allclose(a.step(1), b.step(1), rtol=1e-8)
+        f32 = (t[2].astype(np.float32) / np.float32(255.0)).astype(np.float32)
+        a.set_target(f32)
+        b.set_target(f32)
+        assert np.allclose(a.step(2), b.step(2), rtol=1e-8)
+
+
 def test_mse_tickets_pipeline():
     """gs2d_mse_ticket / gs2d_mse_wait: the loss of iteration i read while iteration i+1 is already enqueued equals
     the loss gs2d_step returns for iteration i; waits may come late and out of order; old tickets expire."""

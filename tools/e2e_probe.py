@@ -1,109 +1,79 @@
-#!/usr/bin/env python
-"""Where the end-to-end step loses time against the device-resident one (developer tool): wall-clock per step of
-loops that add the upload, the conversion and the loss read-back one at a time.
-usage: python tools/e2e_probe.py [size] [splats] [steps]"""
-import importlib, os, sys, time
+"""Where does the end-to-end loop of bench.py lose time against the device-resident run? Same iterations of the C3 fit
+(restart + W warm-up), K steps, wall clock per step for the loop with parts of it left out.
+usage: python tools/e2e_probe.py [S N K W]"""
+import os
+import sys
+import time
+
 import numpy as np
 import torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-gs2d = importlib.import_module("2dgaussiansplatting_b200")
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+from gs2d_loader import gs2d  # noqa: E402
+
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
-N = int(sys.argv[2]) if len(sys.argv) > 2 else 1_000_000
-K = int(sys.argv[3]) if len(sys.argv) > 3 else 30
-rng = np.random.default_rng(0)
-tgt = rng.integers(0, 256, (S, S, 4), dtype=np.uint8)
-pin = torch.from_numpy(tgt.copy()).pin_memory()
+N = int(sys.argv[2]) if len(sys.argv) > 2 else 1000000
+K = int(sys.argv[3]) if len(sys.argv) > 3 else 20
+W = int(sys.argv[4]) if len(sys.argv) > 4 else 5
+
+pin = torch.empty((S, S, 4), dtype=torch.uint8, pin_memory=True)
+pin.numpy()[...] = np.rint(gs2d.synth_target(S, S, seed=1) * 255.0).astype(np.uint8)
+fit = gs2d.Fitter(S, S, N)
+fit.set_target_u8_ptr(pin.data_ptr())
+fit.restart()
+fit.step(3)
 
 
-def timed(name, body, fit):
-    fit.restart()  # every loop times the SAME iterations of the fit (the work per iteration drifts as it converges)
-    fit.step(5)
-    fit.sync()
-    t0 = time.perf_counter()
-    body()
-    fit.sync()
-    print(f"{name:58s} {(time.perf_counter() - t0) * 1e3 / K:.3f} ms/step", flush=True)
-
-
-with gs2d.Fitter(S, S, N) as fit:
-    fit.set_target_u8(tgt)
+def run(name, ticket, upload, adopt=1, block=False):
+    gs2d.set_tuning("GS2D_ADOPT_TARGET", adopt)
+    fit.set_target_u8_ptr(pin.data_ptr())
     fit.restart()
-    fit.set_stats(False)
-    fit.step(5)
-
-    def a():
-        fit.step(K, want_mse=False)
-
-    def b():
-        for _ in range(K):
-            fit.step(1, want_mse=False)
-
-    def c():
-        prev = None
-        for _ in range(K):
-            fit.step(1, want_mse=False)
-            t = fit.mse_ticket()
-            if prev is not None:
-                fit.mse_wait(prev)
-            prev = t
-        fit.mse_wait(prev)
-
-    def d():
-        for _ in range(K):
-            fit.step(1, want_mse=False)
-            fit.set_target_u8_ptr_async(pin.data_ptr())
-
-    def e():
-        prev = None
+    fit.step(W)
+    if upload:
         fit.set_target_u8_ptr_async(pin.data_ptr())
-        for _ in range(K):
-            fit.step(1, want_mse=False)
-            t = fit.mse_ticket()
-            fit.set_target_u8_ptr_async(pin.data_ptr())
-            if prev is not None:
-                fit.mse_wait(prev)
-            prev = t
-        fit.mse_wait(prev)
-
-    def f():
-        for _ in range(K):
-            fit.step(1, want_mse=False)
-            fit.last_mse()
-
-    timed("one gs2d_step(K) call", a, fit)
-    timed("K gs2d_step(1) calls", b, fit)
-    acc = {}
-
-    def call(name, fn, *args):
-        t0 = time.perf_counter()
-        r = fn(*args)
-        acc[name] = acc.get(name, 0.0) + time.perf_counter() - t0
-        return r
-
-    def e_host():
-        prev = None
-        fit.set_target_u8_ptr_async(pin.data_ptr())
-        for _ in range(K):
-            call("step", fit.step, 1, False)
-            t = call("ticket", fit.mse_ticket)
-            call("upload", fit.set_target_u8_ptr_async, pin.data_ptr())
-            if prev is not None:
-                call("wait", fit.mse_wait, prev)
-            prev = t
-        fit.mse_wait(prev)
-
-    timed("e2e loop with host times per call", e_host, fit)
-    print("   host ms per step: " + ", ".join(f"{k} {v * 1e3 / K:.3f}" for k, v in acc.items()))
-    timed("K x (step, ticket, wait previous)", c, fit)
-    timed("K x (step, async upload)", d, fit)
-    timed("K x (step, ticket, async upload, wait previous) = e2e", e, fit)
-    timed("K x (step, last_mse)", f, fit)
-    # the H2D copy alone
-    dst = torch.empty(S * S * 4, dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(10):
-        dst.copy_(pin.view(-1), non_blocking=True)
+    prev = None
+    marks = []
+    for _ in range(K):
+        fit.step(1, want_mse=False)
+        tk = fit.mse_ticket() if ticket else None
+        if upload:
+            fit.set_target_u8_ptr_async(pin.data_ptr())
+        if prev is not None:
+            fit.mse_wait(prev)
+            marks.append(time.perf_counter())
+        prev = tk
+    if prev is not None:
+        fit.mse_wait(prev)
+        marks.append(time.perf_counter())
+    t1 = time.perf_counter()
     torch.cuda.synchronize()
-    dt = (time.perf_counter() - t0) / 10
-    print(f"H2D of {S * S * 4 / 1e6:.0f} MB from pinned memory alone: {dt * 1e3:.3f} ms ({S * S * 4 / dt / 1e9:.1f} GB/s)")
+    t2 = time.perf_counter()
+    d = np.diff(np.asarray(marks)) * 1e3 if len(marks) > 2 else np.zeros(1)
+    print("%-34s %.4f ms/step to last mse, %.4f incl. final sync | between mse arrivals: median %.4f min %.4f max %.4f"
+          % (name, (t1 - t0) * 1e3 / K, (t2 - t0) * 1e3 / K, np.median(d), d.min(), d.max()), flush=True)
+
+
+# device-resident reference: K iterations in one call, CUDA events of the library
+fit.restart()
+fit.step(W - 1)
+torch.cuda.synchronize()
+fit.step(1, want_mse=False)
+fit.step(K, want_mse=False)
+fit.sync()
+print("device-resident (events)           %.4f ms/step" % (fit.last_step_ms() / K), flush=True)
+fit.restart()
+fit.step(W)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+fit.step(K, want_mse=False)
+fit.sync()
+print("device-resident (wall, K in a call) %.4f ms/step" % ((time.perf_counter() - t0) * 1e3 / K), flush=True)
+
+run("steps only", False, False)
+run("steps + tickets", True, False)
+run("steps + uploads", False, True)
+run("steps + tickets + uploads (e2e)", True, True)
+run("the same, staging copied (old)", True, True, adopt=0)
+run("steps + tickets + uploads (e2e)", True, True)
