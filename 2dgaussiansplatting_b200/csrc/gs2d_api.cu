@@ -530,8 +530,14 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMemset( b.rowtab, 0, sizeof( unsigned ) * GS2D_ROWTAB_STRIDE * (size_t)std::max( g.n_total, 1 ) ) );
 	CKC( cudaMemset( b.rowrec, 0xff, sizeof( RowRec ) * (size_t)std::max( g.n_total, 1 ) ) );
 	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
-	// + the 8-byte overflow counter of the slot binning, cleared together with the counters
-	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) ) );
+	// [16-bit counters per (tile, slice) | 8-byte overflow counter of the slot binning | group rows: 32-bit arrival
+	// counters per (group of 4 tiles, slice) | 16-bit totals per bucket in scan order] - the first two (three with group
+	// rows) are cleared by one memset per iteration (launch_preprocess_and_bin)
+	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) +
+	                                    sizeof( unsigned ) * (size_t)( g.nt_pad / 4 ) * g.n_slices +
+	                                    sizeof( unsigned short ) * ( n_buckets + 8 ) ) );
+	// slot rows: 16 bytes per (tile, slice) = group rows: 64 bytes per (group of 4 tiles, slice)
+	static_assert( sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * 4 == sizeof( unsigned ) * 16, "slot rows and group rows share their memory" );
 	CKC( cudaMalloc( &b.bucket_slots, sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * (size_t)g.nt_pad * g.n_slices ) );
 	// cleared once: k_rank loads a bucket's whole 16-byte slot row, of which only the first `count` slots were written
 	CKC( cudaMemset( b.bucket_slots, 0, sizeof( unsigned short ) * GS2D_BUCKET_SLOTS * (size_t)g.nt_pad * g.n_slices ) );

@@ -21,6 +21,7 @@
 // Splat indices are unique inside a bucket, so the sorted lists - and everything downstream - are deterministic
 // although the arrival order inside a bucket is not.
 #include "gs2d_internal.cuh"
+#include "gs2d_bins.cuh"
 
 #define PRE_THREADS 256
 
@@ -49,10 +50,16 @@ struct PairOut
 	// arrivals (rare: 3.3 entries per bucket on average) become triples, appended at *n_over, and go through k_place
 	unsigned short* slots;
 	unsigned long long* n_over;
+	// group rows (GS2D_SLOTS=2, the default; gs2d_bins.cuh): ONE 32-bit atomic and ONE 32-bit store per (splat, group of
+	// four consecutive tiles) instead of one 16-bit store per (splat, tile): the kernel is bound by the number of L2
+	// requests its scattered stores and atomics make (14 M + 4.7 M at 4096^2 / 1 M; now 4.7 M + 4.7 M)
+	unsigned* grp_cnt;           // [nt_pad / 4][n_slices] arrivals of a (group, slice), also those that overflowed
+	unsigned* grp_rows;          // [nt_pad / 4][n_slices][GS2D_GROUP_SLOTS] keys (the memory of `slots`)
+	unsigned long long* ovf64;   // [nt_pad / 4][n_slices] four 16-bit counters: overflow arrivals per tile of the group
 };
 
 // Emit the pairs of tiles id_lo..id_hi (one tile row of one splat) at pos.., one 64-bit atomic per 4-tile group.
-template <bool SLOTS>
+template <int SLOTS>
 __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
                                           int slice, unsigned local, unsigned long long pos,
                                           unsigned long long capacity )
@@ -85,10 +92,52 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 	}
 }
 
+// Group rows (GS2D_SLOTS=2): the arrival of (splat, tiles f0..f1 of group grp) that took position `old` of the row of
+// its (group, slice). Beyond the row: per-tile overflow ranks from one 64-bit atomic, one triple per tile.
+__device__ __forceinline__ void emit_group( const Geometry& g, const PairOut& o, unsigned grp, unsigned f0, unsigned f1,
+                                            unsigned old, int slice, unsigned local, unsigned long long capacity )
+{
+	const size_t pair = (size_t)grp * (unsigned)g.n_slices + (unsigned)slice;
+	if( old < (unsigned)GS2D_GROUP_SLOTS )
+	{
+		o.grp_rows[pair * GS2D_GROUP_SLOTS + old] = group_key( local, f0, f1 - f0 );
+		return;
+	}
+	const unsigned long long oldv = atomicAdd( o.ovf64 + pair, field_ones( f0, f1 ) );
+	for( unsigned f = f0; f <= f1; f++ )
+	{
+		const unsigned bucket = ( grp * 4u + f ) * (unsigned)g.n_slices + (unsigned)slice;
+		const unsigned long long rank = ( oldv >> ( 16u * f ) ) & 0xffffull;
+		const unsigned long long at = atomicAdd( o.n_over, 1ull );
+		if( at < capacity ) // cannot fail: the chunk's pairs were reserved against the capacity
+			__stcs( o.triple + at, (unsigned long long)bucket | ( (unsigned long long)local << 32 ) | ( rank << 48 ) );
+	}
+}
+// one tile row of one splat, tiles id_lo..id_hi. Two groups per step: both atomics are in flight before the first
+// store waits for its position (the emission is bound by the latency of the returning atomics per lane).
+__device__ __forceinline__ void emit_row_groups( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
+                                                 int slice, unsigned local, unsigned long long capacity )
+{
+	const unsigned ns = (unsigned)g.n_slices, g1 = id_hi >> 2;
+	for( unsigned grp = id_lo >> 2; grp <= g1; grp += 2u )
+	{
+		const bool two = grp < g1;
+		unsigned* cnt = o.grp_cnt + (size_t)grp * ns + (unsigned)slice;
+		const unsigned old_a = atomicAdd( cnt, 1u );
+		unsigned old_b = 0u;
+		if( two )
+			old_b = atomicAdd( cnt + ns, 1u );
+		const unsigned fa0 = max( id_lo, grp * 4u ) - grp * 4u, fa1 = min( id_hi, grp * 4u + 3u ) - grp * 4u;
+		emit_group( g, o, grp, fa0, fa1, old_a, slice, local, capacity );
+		if( two ) // the row continues into the next group: it starts at that group's first tile
+			emit_group( g, o, grp + 1u, 0u, min( id_hi, grp * 4u + 7u ) - ( grp * 4u + 4u ), old_b, slice, local, capacity );
+	}
+}
+
 // relaxed: write the record in the scaled form the relaxed-arithmetic blend kernels read (SplatRec, gs2d_internal.cuh)
 // rowtab: 1 = splats of at most GS2D_ROWTAB_STRIDE rows get their rows solved by k_row_table (else every
 // splat is left to the blend kernels' in-kernel solve: GS2D_ROWTAB=0, the A/B reference)
-template <bool SLOTS>
+template <int SLOTS>
 __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, const float* __restrict__ params,
                                                                SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
                                                                PairOut out, unsigned long long capacity, int cull,
@@ -338,7 +387,10 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 				const int ty = o.ty0 + (int)( item - first );
 				const unsigned lo = span & 0xfffu, hi = ( span >> 12 ) & 0xfffu;
 				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-				emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
+				if constexpr( SLOTS == 2 )
+					emit_row_groups( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, capacity );
+				else
+					emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
 				pos += hi - lo + 1u;
 			}
 		}
@@ -396,25 +448,30 @@ __global__ void __launch_bounds__( 256 ) k_row_table( Geometry g, const RowRec* 
 #define SCAN_THREADS 256
 #define SCAN_PER_BLOCK 1024
 // scan index i = tile * n_slices + slice; the 16-bit counter of bucket i lives at cnt16[slice * nt_pad + tile]
+// (group rows: k_group_count has written the totals in scan order, tot16[i])
 __device__ __forceinline__ unsigned bucket_count( const Geometry& g, const unsigned short* __restrict__ cnt16,
-                                                  unsigned i )
+                                                  const unsigned short* __restrict__ tot16, unsigned i )
 {
+	if( tot16 )
+		return tot16[i];
 	const unsigned tile = i / (unsigned)g.n_slices, slice = i - tile * (unsigned)g.n_slices;
 	return cnt16[(size_t)slice * g.nt_pad + tile];
 }
 
 // offset[i] = block-local exclusive scan of the bucket counts; sums[block] = block total
 __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( Geometry g, const unsigned short* __restrict__ cnt16,
+                                                                const unsigned short* __restrict__ tot16,
                                                                 unsigned* __restrict__ offset, unsigned base,
-                                                                unsigned n, unsigned* __restrict__ sums )
+                                                                unsigned n, unsigned n_off, unsigned* __restrict__ sums )
 {
-	// scans the bucket window [base, n): the buckets of this rank's band of tile rows
+	// scans the bucket window [base, n): the buckets of this rank's band of tile rows; offsets are written for
+	// [base, n_off), n_off = n or n + 1 (group rows: the end of the last bucket is looked up as the start of the next)
 	__shared__ unsigned wtot[SCAN_THREADS / 32];
 	const unsigned i0 = base + blockIdx.x * SCAN_PER_BLOCK + threadIdx.x * 4;
 	unsigned v[4];
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
-		v[k] = ( i0 + k < n ) ? bucket_count( g, cnt16, i0 + k ) : 0u;
+		v[k] = ( i0 + k < n ) ? bucket_count( g, cnt16, tot16, i0 + k ) : 0u;
 	unsigned tsum = v[0] + v[1] + v[2] + v[3], incl = tsum;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -440,7 +497,7 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( Geometry g, cons
 #pragma unroll
 	for( int k = 0; k < 4; k++ )
 	{
-		if( i0 + k < n )
+		if( i0 + k < n_off )
 			offset[i0 + k] = run;
 		run += v[k];
 	}
@@ -512,10 +569,25 @@ __global__ void __launch_bounds__( 256 ) k_place( Geometry g, const unsigned lon
                                                   const unsigned* __restrict__ offset,
                                                   const unsigned* __restrict__ sums, unsigned base,
                                                   unsigned* __restrict__ list, const DevState* __restrict__ st,
-                                                  const unsigned long long* __restrict__ n_triples )
+                                                  const unsigned long long* __restrict__ n_triples, int from_end )
 {
 	if( st->need_capacity )
 		return;
+	if( from_end )
+	{
+		// group rows: the triples are the overflow arrivals of their buckets, ranked among themselves; they fill the
+		// bucket from its end (k_rank_groups puts the entries of the row in front of them)
+		const unsigned long long n = *n_triples;
+		const unsigned tpi = (unsigned)( g.tiles_x * g.tiles_y );
+		for( unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n;
+		     i += (unsigned long long)gridDim.x * 256 )
+		{
+			const unsigned long long t = triple[i];
+			list[bucket_offset( offset, sums, (unsigned)t + 1u, base ) - 1u - (unsigned)( t >> 48 )] =
+			    splat_of_triple( g, (unsigned)t, (unsigned)( t >> 32 ) & 0xffffu, tpi );
+		}
+		return;
+	}
 	const unsigned long long n = *n_triples; // all pairs (st->n_keys) or, with slot binning, the overflow arrivals
 	const unsigned long long stride = (unsigned long long)gridDim.x * 256;
 	const unsigned tpi = (unsigned)( g.tiles_x * g.tiles_y );
@@ -636,6 +708,147 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 		}
 }
 
+// ------------------------------------------------------------------------------------- group rows (GS2D_SLOTS=2) ---
+// One thread per (group of four consecutive tiles, index slice), consecutive threads = consecutive slices of a group:
+// the rows (64 bytes), the arrival counters and the overflow words of a warp are contiguous.
+struct GroupWindow
+{
+	unsigned grp_lo, n_pairs;    // pairs [grp_lo * n_slices, .. + n_pairs)
+	unsigned tile_lo, tile_hi;   // tiles of this rank's band: what the scan covers
+};
+// the keys of one row: only the 32-byte sectors that hold entries are fetched
+__device__ __forceinline__ void load_row( unsigned* w, const unsigned* __restrict__ rows, size_t pair, unsigned c )
+{
+	const uint4* r = reinterpret_cast<const uint4*>( rows ) + pair * ( GS2D_GROUP_SLOTS / 4 );
+	uint4 q[4] = { make_uint4( 0u, 0u, 0u, 0u ), make_uint4( 0u, 0u, 0u, 0u ), make_uint4( 0u, 0u, 0u, 0u ),
+	               make_uint4( 0u, 0u, 0u, 0u ) };
+	if( c > 0u )
+	{
+		q[0] = __ldcs( r );
+		q[1] = __ldcs( r + 1 );
+	}
+	if( c > 8u )
+	{
+		q[2] = __ldcs( r + 2 );
+		q[3] = __ldcs( r + 3 );
+	}
+#pragma unroll
+	for( int i = 0; i < 4; i++ )
+	{
+		w[4 * i] = q[i].x;
+		w[4 * i + 1] = q[i].y;
+		w[4 * i + 2] = q[i].z;
+		w[4 * i + 3] = q[i].w;
+	}
+}
+
+// entries per (tile, slice) bucket in scan order: what the exclusive scan turns into the list offsets
+__global__ void __launch_bounds__( 256 ) k_group_count( Geometry g, const unsigned* __restrict__ grp_cnt,
+                                                        const unsigned* __restrict__ rows,
+                                                        const unsigned long long* __restrict__ ovf64,
+                                                        unsigned short* __restrict__ tot16, GroupWindow win )
+{
+	const unsigned p = blockIdx.x * 256u + threadIdx.x;
+	if( p >= win.n_pairs )
+		return;
+	const unsigned ns = (unsigned)g.n_slices;
+	const size_t pair = (size_t)win.grp_lo * ns + p;
+	const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair - (size_t)grp * ns );
+	const unsigned c_raw = grp_cnt[pair], c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
+	unsigned w[GS2D_GROUP_SLOTS], n[4];
+	load_row( w, rows, pair, c );
+	group_counts( w, c, n );
+	if( c_raw > (unsigned)GS2D_GROUP_SLOTS )
+	{
+		const unsigned long long ov = ovf64[pair];
+#pragma unroll
+		for( unsigned f = 0; f < 4u; f++ )
+			n[f] += (unsigned)( ov >> ( 16u * f ) ) & 0xffffu;
+	}
+#pragma unroll
+	for( unsigned f = 0; f < 4u; f++ )
+	{
+		const unsigned tile = grp * 4u + f;
+		if( tile >= win.tile_lo && tile < win.tile_hi )
+			tot16[(size_t)tile * ns + slice] = (unsigned short)n[f];
+	}
+}
+
+// The lists of the four tiles of a group, ordered by splat index: sort the row's keys once, deal them to the tiles
+// they cover (gs2d_bins.cuh). A bucket with overflow arrivals (k_place put them at its end) is joined in the
+// unordered list and ranked by counting, like the sort-free path does for every long bucket.
+__global__ void __launch_bounds__( 256 ) k_rank_groups( Geometry g, const unsigned* __restrict__ grp_cnt,
+                                                        const unsigned* __restrict__ rows,
+                                                        const unsigned long long* __restrict__ ovf64,
+                                                        const unsigned* __restrict__ offset,
+                                                        const unsigned* __restrict__ sums, unsigned* __restrict__ list,
+                                                        unsigned* __restrict__ out, uint2* __restrict__ tile_range,
+                                                        unsigned base, GroupWindow win, const DevState* __restrict__ st )
+{
+	if( st->need_capacity )
+		return;
+	const unsigned p = blockIdx.x * 256u + threadIdx.x;
+	const bool valid = p < win.n_pairs; // no early exit: the warp votes below
+	const unsigned ns = (unsigned)g.n_slices;
+	const size_t pair = (size_t)win.grp_lo * ns + ( valid ? p : 0u );
+	const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair - (size_t)grp * ns );
+	const unsigned c_raw = valid ? grp_cnt[pair] : 0u, c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
+	const unsigned tpi = (unsigned)( g.tiles_x * g.tiles_y );
+	unsigned start[4], first[4];
+	bool in[4];
+#pragma unroll
+	for( unsigned f = 0; f < 4u; f++ )
+	{
+		const unsigned tile = grp * 4u + f;
+		in[f] = valid && tile >= win.tile_lo && tile < win.tile_hi;
+		start[f] = in[f] ? bucket_offset( offset, sums, tile * ns + slice, base ) : 0u;
+		first[f] = ( tile / tpi ) * (unsigned)g.n_splats + slice * (unsigned)g.slice_size;
+	}
+	unsigned w[GS2D_GROUP_SLOTS], e[GS2D_GROUP_SLOTS];
+	load_row( w, rows, pair, c );
+	const unsigned long long ov = c_raw > (unsigned)GS2D_GROUP_SLOTS ? ovf64[pair] : 0ull;
+	row_keys( e, w, c );
+	sort8_keys( e );
+	if( __any_sync( 0xffffffffu, c > 8u ) )
+	{
+		sort8_keys( e + 8 );
+		merge16_keys( e );
+	}
+	unsigned* dst[4];
+	unsigned novf[4], pos[4] = { 0u, 0u, 0u, 0u };
+#pragma unroll
+	for( unsigned f = 0; f < 4u; f++ )
+	{
+		novf[f] = (unsigned)( ov >> ( 16u * f ) ) & 0xffffu;
+		dst[f] = in[f] ? ( novf[f] ? list : out ) + start[f] : nullptr;
+	}
+	group_deal( e, c, dst, first, pos );
+#pragma unroll
+	for( unsigned f = 0; f < 4u; f++ )
+	{
+		if( !in[f] )
+			continue;
+		const unsigned tile = grp * 4u + f, n = pos[f] + novf[f];
+		if( slice == 0u )
+			tile_range[tile].x = start[f];
+		if( slice == ns - 1u )
+			tile_range[tile].y = start[f] + n;
+		if( novf[f] )
+		{
+			const unsigned* pl = list + start[f];
+			unsigned* q = out + start[f];
+			for( unsigned a = 0; a < n; a++ )
+			{
+				const unsigned ea = pl[a];
+				unsigned r = 0;
+				for( unsigned b = 0; b < n; b++ )
+					r += pl[b] < ea ? 1u : 0u;
+				q[r] = ea;
+			}
+		}
+	}
+}
+
 // ---------------------------------------------------------------------------------------------------- launch ---
 bool gs2d_exact_mode() { return gs2d_tune( "GS2D_EXACT", 0 ) != 0; }
 
@@ -653,24 +866,38 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		return 0;
 	}
 	const unsigned nbk = (unsigned)g.n_tiles_total * (unsigned)g.n_slices;
-	cudaMemsetAsync( b.bucket_cnt, 0, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ), s );
-	if( b.touch )
-		cudaMemsetAsync( b.touch, 0, sizeof( unsigned ) * ( (size_t)g.n_pad / 128 + 1 ), s );
-	const bool slots = use_slots && gs2d_tune( "GS2D_SLOTS", 1 ) != 0;
+	// 0: every pair a triple; 1: slot rows per (tile, slice); 2: group rows (gs2d_bins.cuh), the default
+	const int mode = use_slots ? gs2d_tune( "GS2D_SLOTS", 2 ) : 0;
+	const bool slots = mode != 0;
+	const size_t n_cnt16 = (size_t)g.nt_pad * g.n_slices, n_pairs_all = (size_t)( g.nt_pad / 4 ) * g.n_slices;
 	PairOut po;
 	po.triple = b.triples;
 	po.cnt64 = reinterpret_cast<unsigned long long*>( b.bucket_cnt );
 	po.slots = b.bucket_slots;
-	// the overflow counter sits behind the bucket counters and is cleared with them
-	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + (size_t)g.nt_pad * g.n_slices );
+	// the overflow counter sits behind the bucket counters and is cleared with them; behind it the arrival counters
+	// of the group rows (cleared too when they are in use) and the totals in scan order (every one is written)
+	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + n_cnt16 );
+	po.grp_cnt = reinterpret_cast<unsigned*>( po.n_over + 1 );
+	po.grp_rows = reinterpret_cast<unsigned*>( b.bucket_slots );
+	po.ovf64 = po.cnt64;
+	unsigned short* tot16 = reinterpret_cast<unsigned short*>( po.grp_cnt + n_pairs_all );
+	cudaMemsetAsync( b.bucket_cnt, 0,
+	                 sizeof( unsigned short ) * n_cnt16 + sizeof( unsigned long long ) +
+	                     ( mode == 2 ? sizeof( unsigned ) * n_pairs_all : 0 ),
+	                 s );
+	if( b.touch )
+		cudaMemsetAsync( b.touch, 0, sizeof( unsigned ) * ( (size_t)g.n_pad / 128 + 1 ), s );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
 	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
-	if( slots )
-		k_preprocess<true><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                               relaxed, rowtab, b.touch, b.reach, b.state );
+	if( mode == 2 )
+		k_preprocess<2><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		                                            relaxed, rowtab, b.touch, b.reach, b.state );
+	else if( slots )
+		k_preprocess<1><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		                                            relaxed, rowtab, b.touch, b.reach, b.state );
 	else
-		k_preprocess<false><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                                relaxed, rowtab, b.touch, b.reach, b.state );
+		k_preprocess<0><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		                                            relaxed, rowtab, b.touch, b.reach, b.state );
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
@@ -709,20 +936,40 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		join();
 		return launches;
 	}
+	if( mode == 2 )
+	{
+		GroupWindow win;
+		win.tile_lo = lo / (unsigned)g.n_slices;
+		win.tile_hi = hi / (unsigned)g.n_slices;
+		win.grp_lo = win.tile_lo >> 2;
+		win.n_pairs = ( ( ( win.tile_hi + 3u ) >> 2 ) - win.grp_lo ) * (unsigned)g.n_slices;
+		const unsigned pair_nb = ( win.n_pairs + 255u ) / 256u;
+		// one more scan item than buckets: the end of the window's last bucket
+		const unsigned scan_nb = ( hi - lo + 1u + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+		k_group_count<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, tot16, win );
+		k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, tot16, b.bucket_off, lo, hi, hi + 1u, b.scan_sums );
+		k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
+		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over, 1 );
+		k_rank_groups<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, b.bucket_off, b.scan_sums, b.vals[1],
+		                                       b.vals[0], b.tile_range, lo, win, b.state );
+		launches += 5;
+		join();
+		return launches;
+	}
 	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
-	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, b.bucket_off, lo, hi, b.scan_sums );
+	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, nullptr, b.bucket_off, lo, hi, hi, b.scan_sums );
 	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
 	if( slots )
 	{
 		// few triples, if any: a small grid (the kernel is a grid-stride loop over *n_over)
-		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over );
+		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over, 0 );
 		k_rank<true><<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1],
 		                                                     b.vals[0], b.tile_range, lo, hi, b.state, b.bucket_slots );
 	}
 	else
 	{
 		k_place<<<148 * 16, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state,
-		                                  &b.state->n_keys );
+		                                  &b.state->n_keys, 0 );
 		k_rank<false><<<( hi - lo + 255 ) / 256, 256, 0, s>>>( g, b.bucket_cnt, b.bucket_off, b.scan_sums, b.vals[1],
 		                                                      b.vals[0], b.tile_range, lo, hi, b.state, nullptr );
 	}

@@ -321,28 +321,40 @@ def test_ellipse_culling_is_a_superset_of_the_footprint():
 
 
 def test_slot_binning_equals_the_triple_path():
-    """Slot binning (first 8 arrivals of a (tile, slice) bucket stored straight into the bucket's slot row, the rest
-    through k_place) must build the same ordered lists as the triple path: bit-identical images, same live pairs and
-    list entries - also with hundreds of entries per bucket (every bucket overflows its slot row)."""
-    W, H = 700, 520
+    """The three binning paths must build the same ordered lists: GS2D_SLOTS=0 (every pair a triple through k_place),
+    1 (the first 8 arrivals of a (tile, slice) bucket stored into the bucket's slot row) and 2 (the default: one key
+    per (Gaussian, group of 4 tiles) in a 16-slot row, sorted once per group, gs2d_bins.cuh) - bit-identical images,
+    same live pairs and list entries, the same loss after three iterations - with a few entries per bucket, with
+    hundreds (every row overflows), with an image width whose tile rows straddle the groups of four tiles, and on a
+    rank's band of tile rows."""
     rng = np.random.default_rng(21)
-    cases = [random_splats(rng, W, H, 6000, smin=2, smax=14), random_splats(rng, W, H, 1500, smin=100, smax=900,
-                                                                          opacity=(0.1, 0.3))]
-    for splats in cases:
+    cases = [(700, 520, random_splats(rng, 700, 520, 6000, smin=2, smax=14), None),
+             (700, 520, random_splats(rng, 700, 520, 1500, smin=100, smax=900, opacity=(0.1, 0.3)), None),
+             (330, 250, random_splats(rng, 330, 250, 5000, smin=1, smax=30), None),   # 21 tiles per tile row
+             (40, 400, random_splats(rng, 40, 400, 3000, smin=1, smax=20), None),     # 3 tiles per tile row
+             (700, 520, random_splats(rng, 700, 520, 6000, smin=2, smax=30), (1, 3))]
+    for W, H, splats, band in cases:
         out = []
-        for slots in (0, 1):
+        for slots in (0, 1, 2):
             gs2d.set_tuning("GS2D_SLOTS", slots)
             try:
                 with gs2d.Fitter(W, H, len(splats)) as fit:
                     fit.set_target(gs2d.synth_target(W, H, seed=3))
                     fit.upload(splats)
+                    if band:
+                        fit.set_band(*band)
                     fit.forward()
-                    out.append((fit.image(), fit.stats()))
+                    img, st = fit.image(), fit.stats()
+                    mse = fit.step(3)[:, 0]
+                    out.append((img, st, mse))
             finally:
-                gs2d.set_tuning("GS2D_SLOTS", 1)
-        (img0, st0), (img1, st1) = out
-        assert img0.tobytes() == img1.tobytes()
-        assert st0["live_pairs"] == st1["live_pairs"] and st0["keys"] == st1["keys"]
+                gs2d.set_tuning("GS2D_SLOTS", 2)
+        img0, st0, mse0 = out[0]
+        assert st0["keys"] > 0
+        for img, st, mse in out[1:]:
+            assert img0.tobytes() == img.tobytes()
+            assert st0["live_pairs"] == st["live_pairs"] and st0["keys"] == st["keys"]
+            assert mse0[0] == mse[0] and np.allclose(mse0, mse, rtol=1e-6)
 
 
 def test_row_table_equals_the_in_kernel_solve():

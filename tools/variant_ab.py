@@ -15,7 +15,7 @@ OUT = sys.argv[1]
 VARIANTS = sys.argv[2:] or ["default"]
 S, N, K = int(os.environ.get("AB_SIZE", 4096)), int(os.environ.get("AB_SPLATS", 1_000_000)), int(os.environ.get("AB_ITERS", 30))
 KNOBS = sorted({kv.split("=")[0] for v in VARIANTS if v != "default" for kv in v.split(",")})
-DEFAULTS = {"GS2D_PDL": 1, "GS2D_SLOTS": 1, "GS2D_GRAPH": 1, "GS2D_CULL": 1, "GS2D_EXACT": 0, "GS2D_ROWTAB": 1,
+DEFAULTS = {"GS2D_PDL": 1, "GS2D_SLOTS": 2, "GS2D_GRAPH": 1, "GS2D_CULL": 1, "GS2D_EXACT": 0, "GS2D_ROWTAB": 1,
             "GS2D_SIDE_STREAM": 1}
 
 
