@@ -95,12 +95,14 @@ __device__ __forceinline__ void emit_row( const Geometry& g, const PairOut& o, u
 // Group rows (GS2D_SLOTS=2): the arrival of (splat, tiles f0..f1 of group grp) that took position `old` of the row of
 // its (group, slice). Beyond the row: per-tile overflow ranks from one 64-bit atomic, one triple per tile.
 __device__ __forceinline__ void emit_group( const Geometry& g, const PairOut& o, unsigned grp, unsigned f0, unsigned f1,
-                                            unsigned old, int slice, unsigned local, unsigned long long capacity )
+                                            unsigned old, int slice, unsigned local, unsigned long long capacity,
+                                            int probe = 0 )
 {
 	const size_t pair = (size_t)grp * (unsigned)g.n_slices + (unsigned)slice;
 	if( old < (unsigned)GS2D_GROUP_SLOTS )
 	{
-		o.grp_rows[pair * GS2D_GROUP_SLOTS + old] = group_key( local, f0, f1 - f0 );
+		if( !( probe & 1 ) )
+			o.grp_rows[pair * GS2D_GROUP_SLOTS + old] = group_key( local, f0, f1 - f0 );
 		return;
 	}
 	const unsigned long long oldv = atomicAdd( o.ovf64 + pair, field_ones( f0, f1 ) );
@@ -115,22 +117,24 @@ __device__ __forceinline__ void emit_group( const Geometry& g, const PairOut& o,
 }
 // one tile row of one splat, tiles id_lo..id_hi. Two groups per step: both atomics are in flight before the first
 // store waits for its position (the emission is bound by the latency of the returning atomics per lane).
+// probe (developer timing knob GS2D_K1_PROBE, results WRONG when set): 1 = no key stores, 2 = no atomics
 __device__ __forceinline__ void emit_row_groups( const Geometry& g, const PairOut& o, unsigned id_lo, unsigned id_hi,
-                                                 int slice, unsigned local, unsigned long long capacity )
+                                                 int slice, unsigned local, unsigned long long capacity, int probe )
 {
 	const unsigned ns = (unsigned)g.n_slices, g1 = id_hi >> 2;
 	for( unsigned grp = id_lo >> 2; grp <= g1; grp += 2u )
 	{
 		const bool two = grp < g1;
 		unsigned* cnt = o.grp_cnt + (size_t)grp * ns + (unsigned)slice;
-		const unsigned old_a = atomicAdd( cnt, 1u );
-		unsigned old_b = 0u;
-		if( two )
+		const unsigned old_a = ( probe & 2 ) ? ( local & 7u ) : atomicAdd( cnt, 1u );
+		unsigned old_b = ( probe & 2 ) ? ( local & 7u ) : 0u;
+		if( two && !( probe & 2 ) )
 			old_b = atomicAdd( cnt + ns, 1u );
 		const unsigned fa0 = max( id_lo, grp * 4u ) - grp * 4u, fa1 = min( id_hi, grp * 4u + 3u ) - grp * 4u;
-		emit_group( g, o, grp, fa0, fa1, old_a, slice, local, capacity );
+		emit_group( g, o, grp, fa0, fa1, old_a, slice, local, capacity, probe );
 		if( two ) // the row continues into the next group: it starts at that group's first tile
-			emit_group( g, o, grp + 1u, 0u, min( id_hi, grp * 4u + 7u ) - ( grp * 4u + 4u ), old_b, slice, local, capacity );
+			emit_group( g, o, grp + 1u, 0u, min( id_hi, grp * 4u + 7u ) - ( grp * 4u + 4u ), old_b, slice, local, capacity,
+			            probe );
 	}
 }
 
@@ -274,7 +278,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 			sb.k.inv_a = 1.0f / a;
 			sb.k.vx_max = hx; // 3 * sqrt( cov[0][0] ) == 3 * sqrt( d / (a d - b^2) )
 			sb.k.vy_at = -b * hx / d;
-			sb.k.delta = span_delta( px, hx, cull );
+			sb.k.delta = span_delta( px, hx, cull & 1 );
 			sb.k.begY = begY;
 			sb.k.endY = endY;
 		}
@@ -388,7 +392,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 				const unsigned lo = span & 0xfffu, hi = ( span >> 12 ) & 0xfffu;
 				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
 				if constexpr( SLOTS == 2 )
-					emit_row_groups( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, capacity );
+					emit_row_groups( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, capacity, cull >> 8 );
 				else
 					emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
 				pos += hi - lo + 1u;
@@ -711,6 +715,17 @@ __global__ void __launch_bounds__( 256 ) k_rank( Geometry g, const unsigned shor
 // ------------------------------------------------------------------------------------- group rows (GS2D_SLOTS=2) ---
 // One thread per (group of four consecutive tiles, index slice), consecutive threads = consecutive slices of a group:
 // the rows (64 bytes), the arrival counters and the overflow words of a warp are contiguous.
+// store into the block's staging array through its 32-bit shared-memory address (a generic pointer makes the
+// compiler rebuild the shared window's base in front of every predicated store)
+struct PutShared
+{
+	enum { SCALE = 4 }; // positions are byte addresses
+	__device__ __forceinline__ void operator()( unsigned at, unsigned v ) const
+	{
+		asm volatile( "st.shared.u32 [%0], %1;" ::"r"( at ), "r"( v ) : "memory" );
+	}
+};
+#define RANK_STAGE 8192 // list entries a block of k_rank_groups can stage in shared memory (32 KB)
 struct GroupWindow
 {
 	unsigned grp_lo, n_pairs;    // pairs [grp_lo * n_slices, .. + n_pairs)
@@ -749,15 +764,14 @@ __global__ void __launch_bounds__( 256 ) k_group_count( Geometry g, const unsign
                                                         unsigned short* __restrict__ tot16, GroupWindow win )
 {
 	const unsigned p = blockIdx.x * 256u + threadIdx.x;
-	if( p >= win.n_pairs )
-		return;
+	const bool valid = p < win.n_pairs; // no early exit: the warp votes below
 	const unsigned ns = (unsigned)g.n_slices;
-	const size_t pair = (size_t)win.grp_lo * ns + p;
+	const size_t pair = (size_t)win.grp_lo * ns + ( valid ? p : 0u );
 	const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair - (size_t)grp * ns );
-	const unsigned c_raw = grp_cnt[pair], c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
+	const unsigned c_raw = valid ? grp_cnt[pair] : 0u, c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
 	unsigned w[GS2D_GROUP_SLOTS], n[4];
 	load_row( w, rows, pair, c );
-	group_counts( w, c, n );
+	group_counts( w, c, __reduce_max_sync( 0xffffffffu, c ), n );
 	if( c_raw > (unsigned)GS2D_GROUP_SLOTS )
 	{
 		const unsigned long long ov = ovf64[pair];
@@ -769,7 +783,7 @@ __global__ void __launch_bounds__( 256 ) k_group_count( Geometry g, const unsign
 	for( unsigned f = 0; f < 4u; f++ )
 	{
 		const unsigned tile = grp * 4u + f;
-		if( tile >= win.tile_lo && tile < win.tile_hi )
+		if( valid && tile >= win.tile_lo && tile < win.tile_hi )
 			tot16[(size_t)tile * ns + slice] = (unsigned short)n[f];
 	}
 }
@@ -788,8 +802,26 @@ __global__ void __launch_bounds__( 256 ) k_rank_groups( Geometry g, const unsign
 	if( st->need_capacity )
 		return;
 	const unsigned p = blockIdx.x * 256u + threadIdx.x;
-	const bool valid = p < win.n_pairs; // no early exit: the warp votes below
+	const bool valid = p < win.n_pairs; // no early exit: the warp votes and the block synchronises below
 	const unsigned ns = (unsigned)g.n_slices;
+	// A block that holds whole groups (all slices of 256 / n_slices groups) writes ONE contiguous piece of the lists:
+	// the entries are dealt into shared memory and leave in full 128-byte lines. Dealt straight to global memory, a
+	// warp's store of "entry i of tile f" touches ~13 sectors with a few bytes each, and the kernel ran at the L2
+	// request rate (77 us for 56 MB of lists) like the emission it replaced.
+	__shared__ unsigned sm_out[RANK_STAGE];
+	unsigned blk_base = 0u, blk_n = 0u;
+	bool staged = false;
+	if( ns <= 256u )
+	{
+		const unsigned gpb = 256u / ns, grp_a = win.grp_lo + blockIdx.x * gpb;
+		const unsigned t_a = max( grp_a * 4u, win.tile_lo ), t_b = min( ( grp_a + gpb ) * 4u, win.tile_hi );
+		if( t_a < t_b )
+		{
+			blk_base = bucket_offset( offset, sums, t_a * ns, base );
+			blk_n = bucket_offset( offset, sums, t_b * ns, base ) - blk_base;
+			staged = blk_n <= (unsigned)RANK_STAGE;
+		}
+	}
 	const size_t pair = (size_t)win.grp_lo * ns + ( valid ? p : 0u );
 	const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair - (size_t)grp * ns );
 	const unsigned c_raw = valid ? grp_cnt[pair] : 0u, c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
@@ -808,35 +840,47 @@ __global__ void __launch_bounds__( 256 ) k_rank_groups( Geometry g, const unsign
 	load_row( w, rows, pair, c );
 	const unsigned long long ov = c_raw > (unsigned)GS2D_GROUP_SLOTS ? ovf64[pair] : 0ull;
 	row_keys( e, w, c );
+	const unsigned c_max = __reduce_max_sync( 0xffffffffu, c );
 	sort8_keys( e );
-	if( __any_sync( 0xffffffffu, c > 8u ) )
+	if( c_max > 8u )
 	{
 		sort8_keys( e + 8 );
 		merge16_keys( e );
 	}
-	unsigned* dst[4];
-	unsigned novf[4], pos[4] = { 0u, 0u, 0u, 0u };
-#pragma unroll
-	for( unsigned f = 0; f < 4u; f++ )
+	unsigned pos[4] = { 0u, 0u, 0u, 0u };
+	if( staged )
 	{
-		novf[f] = (unsigned)( ov >> ( 16u * f ) ) & 0xffffu;
-		dst[f] = in[f] ? ( novf[f] ? list : out ) + start[f] : nullptr;
+		unsigned off[4];
+#pragma unroll
+		for( unsigned f = 0; f < 4u; f++ )
+			off[f] = start[f] - blk_base;
+		unsigned sm_addr = (unsigned)__cvta_generic_to_shared( sm_out );
+		asm volatile( "" : "+r"( sm_addr ) ); // kept in a register (else rebuilt from the CTA id in front of every store)
+#pragma unroll
+		for( unsigned f = 0; f < 4u; f++ )
+			off[f] = sm_addr + off[f] * 4u;
+		group_deal( e, c, c_max, PutShared{}, off, in, first, pos );
 	}
-	group_deal( e, c, dst, first, pos );
+	else
+		group_deal( e, c, c_max, PutArray{ out }, start, in, first, pos );
 #pragma unroll
 	for( unsigned f = 0; f < 4u; f++ )
 	{
 		if( !in[f] )
 			continue;
-		const unsigned tile = grp * 4u + f, n = pos[f] + novf[f];
+		const unsigned tile = grp * 4u + f, novf = (unsigned)( ov >> ( 16u * f ) ) & 0xffffu, n = pos[f] + novf;
 		if( slice == 0u )
 			tile_range[tile].x = start[f];
 		if( slice == ns - 1u )
 			tile_range[tile].y = start[f] + n;
-		if( novf[f] )
+		if( novf )
 		{
-			const unsigned* pl = list + start[f];
-			unsigned* q = out + start[f];
+			// rare: the entries of the row join the bucket's overflow arrivals (k_place put those at its end) in the
+			// unordered list; then rank by counting, like the sort-free path does for every long bucket
+			unsigned* q = staged ? sm_out + ( start[f] - blk_base ) : out + start[f];
+			unsigned* pl = list + start[f];
+			for( unsigned a = 0; a < pos[f]; a++ )
+				pl[a] = q[a];
 			for( unsigned a = 0; a < n; a++ )
 			{
 				const unsigned ea = pl[a];
@@ -846,6 +890,12 @@ __global__ void __launch_bounds__( 256 ) k_rank_groups( Geometry g, const unsign
 				q[r] = ea;
 			}
 		}
+	}
+	if( staged )
+	{
+		__syncthreads();
+		for( unsigned i = threadIdx.x; i < blk_n; i += 256u )
+			out[blk_base + i] = sm_out[i];
 	}
 }
 
@@ -890,7 +940,8 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
 	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
 	if( mode == 2 )
-		k_preprocess<2><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
+		k_preprocess<2><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity,
+		                                            gs2d_tune( "GS2D_CULL", 1 ) | ( gs2d_tune( "GS2D_K1_PROBE", 0 ) << 8 ),
 		                                            relaxed, rowtab, b.touch, b.reach, b.state );
 	else if( slots )
 		k_preprocess<1><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),

@@ -67,39 +67,73 @@ __device__ __forceinline__ void row_keys( unsigned* e, const unsigned* w, unsign
 		e[i] = (unsigned)i < c ? w[i] : GS2D_KEY_NONE;
 }
 
-// entries of the four tiles of the group among the row's c keys (any order)
-__device__ __forceinline__ void group_counts( const unsigned* e, unsigned c, unsigned* n )
+// entries of the four tiles of the group among the row's c keys (any order); c_max >= c bounds the work in steps of
+// four keys (the device passes the maximum over the warp, so the skip is a uniform branch).
+// The 4-bit mask of the fields a key covers is spread to one byte per field (bit k -> bit 8k: the four partial
+// products of m * 0x00204081 never meet in a bit position, so there are no carries) and added: four counters per add.
+__device__ __forceinline__ void group_counts( const unsigned* e, unsigned c, unsigned c_max, unsigned* n )
 {
-	n[0] = n[1] = n[2] = n[3] = 0u;
+	unsigned acc = 0u;
 #pragma unroll
-	for( int i = 0; i < GS2D_GROUP_SLOTS; i++ )
+	for( int i0 = 0; i0 < GS2D_GROUP_SLOTS; i0 += 4 )
 	{
-		if( (unsigned)i >= c )
+		if( (unsigned)i0 >= c_max )
 			break;
 #pragma unroll
-		for( unsigned f = 0; f < 4u; f++ )
-			n[f] += key_covers( e[i], f ) ? 1u : 0u;
+		for( int i = i0; i < i0 + 4; i++ )
+		{
+			const unsigned key = e[i];
+			const unsigned m = ( ( 2u << ( key & 3u ) ) - 1u ) << ( ( key >> 2 ) & 3u ); // fields f0 .. f0 + ext (<= 3)
+			acc += (unsigned)i < c ? ( ( m * 0x00204081u ) & 0x01010101u ) : 0u;
+		}
 	}
+	n[0] = acc & 0xffu;
+	n[1] = ( acc >> 8 ) & 0xffu;
+	n[2] = ( acc >> 16 ) & 0xffu;
+	n[3] = acc >> 24;
 }
 
-// Deal the sorted keys to the lists of the four tiles: dst[f][pos[f]++] = first[f] + index inside the slice for every
-// tile f the key covers (dst[f] == nullptr: the tile is outside the window, its entries - there are none - are skipped).
-// pos[] must come in as 0 and returns the number of entries written per tile.
-__device__ __forceinline__ void group_deal( const unsigned* e, unsigned c, unsigned* const* dst, const unsigned* first,
-                                            unsigned* pos )
+// Deal the sorted keys to the lists of the four tiles: base[off[f] + pos[f]++] = first[f] + index inside the slice for
+// every tile f the key covers and that is inside the window (in[f]). pos[] must come in as 0 and returns the number
+// of entries written per tile. c_max: as above.
+// The four running positions live in the bytes of one word, like group_counts' counters (a row deals at most 16
+// entries to a tile): one add per key advances all four, and byte f is the position of the key in tile f's list.
+// put( off[f] + Put::SCALE * position, value ) stores one list entry (the device's shared-memory store works on byte
+// addresses, SCALE = 4; the global-memory store and the host's on array indices).
+template <class Put>
+__device__ __forceinline__ void group_deal( const unsigned* e, unsigned c, unsigned c_max, const Put& put,
+                                            const unsigned* off, const bool* in, const unsigned* first, unsigned* pos )
 {
+	// byte f of acc = Put::SCALE * entries dealt to tile f so far (at most 16 * 4)
+	unsigned acc = 0u;
+	const unsigned window = ( in[0] ? 1u : 0u ) | ( in[1] ? 2u : 0u ) | ( in[2] ? 4u : 0u ) | ( in[3] ? 8u : 0u );
 #pragma unroll
-	for( int i = 0; i < GS2D_GROUP_SLOTS; i++ )
+	for( int i0 = 0; i0 < GS2D_GROUP_SLOTS; i0 += 4 )
 	{
-		if( (unsigned)i >= c )
+		if( (unsigned)i0 >= c_max )
 			break;
-		const unsigned key = e[i], local = key_local( key );
 #pragma unroll
-		for( unsigned f = 0; f < 4u; f++ )
-			if( key_covers( key, f ) && dst[f] )
-			{
-				dst[f][pos[f]] = first[f] + local;
-				pos[f]++;
-			}
+		for( int i = i0; i < i0 + 4; i++ )
+		{
+			const unsigned key = e[i], local = key_local( key );
+			// fields f0 .. f0 + ext (<= 3) inside the window; nothing for a slot beyond the row's entries
+			const unsigned m = (unsigned)i < c ? ( ( ( ( 2u << ( key & 3u ) ) - 1u ) << ( ( key >> 2 ) & 3u ) ) & window ) : 0u;
+#pragma unroll
+			for( unsigned f = 0; f < 4u; f++ )
+				if( m & ( 1u << f ) )
+					put( off[f] + ( ( acc >> ( 8u * f ) ) & 0xffu ), first[f] + local );
+			acc += ( ( m * 0x00204081u ) & 0x01010101u ) * (unsigned)Put::SCALE;
+		}
 	}
+	pos[0] = ( acc & 0xffu ) / (unsigned)Put::SCALE;
+	pos[1] = ( ( acc >> 8 ) & 0xffu ) / (unsigned)Put::SCALE;
+	pos[2] = ( ( acc >> 16 ) & 0xffu ) / (unsigned)Put::SCALE;
+	pos[3] = ( acc >> 24 ) / (unsigned)Put::SCALE;
 }
+// the plain store
+struct PutArray
+{
+	enum { SCALE = 1 };
+	unsigned* base;
+	__device__ __forceinline__ void operator()( unsigned at, unsigned v ) const { base[at] = v; }
+};

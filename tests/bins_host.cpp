@@ -61,7 +61,7 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 		const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair % ns );
 		const unsigned c_raw = grp_cnt[pair], c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
 		unsigned n[4];
-		group_counts( &rows[pair * GS2D_GROUP_SLOTS], c, n );
+		group_counts( &rows[pair * GS2D_GROUP_SLOTS], c, c, n );
 		if( c_raw > (unsigned)GS2D_GROUP_SLOTS )
 			for( unsigned f = 0; f < 4u; f++ )
 				n[f] += (unsigned)( ovf64[pair] >> ( 16u * f ) ) & 0xffffu;
@@ -101,7 +101,6 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 			merge16_keys( e );
 		}
 		const unsigned long long ov = c_raw > (unsigned)GS2D_GROUP_SLOTS ? ovf64[pair] : 0ull;
-		unsigned* dst[4];
 		unsigned first[4], start[4], novf[4], pos[4] = { 0u, 0u, 0u, 0u };
 		bool in[4];
 		for( unsigned f = 0; f < 4u; f++ )
@@ -111,9 +110,8 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 			start[f] = in[f] ? offset[tile * ns + slice] : 0u;
 			first[f] = slice * (unsigned)slice_size;
 			novf[f] = (unsigned)( ov >> ( 16u * f ) ) & 0xffffu;
-			dst[f] = in[f] ? ( novf[f] ? list.data() : out_list ) + start[f] : nullptr;
 		}
-		group_deal( e, c, dst, first, pos );
+		group_deal( e, c, c, PutArray{ out_list }, start, in, first, pos );
 		for( unsigned f = 0; f < 4u; f++ )
 		{
 			if( !in[f] )
@@ -125,6 +123,9 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 				tile_range[2 * tile + 1] = start[f] + n;
 			if( novf[f] )
 			{
+				// the entries of the row join the overflow arrivals in the unordered list, then everything is ranked
+				for( unsigned a = 0; a < pos[f]; a++ )
+					list[start[f] + a] = out_list[start[f] + a];
 				const unsigned* pl = list.data() + start[f];
 				for( unsigned a = 0; a < n; a++ )
 				{
