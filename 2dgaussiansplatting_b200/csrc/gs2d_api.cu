@@ -392,7 +392,7 @@ extern "C" void gs2d_destroy( gs2d_ctx* c )
 	if( c->side.ev_join )
 		cudaEventDestroy( c->side.ev_join );
 	void* ptrs[] = { b.params,     b.grads,  b.adam_m, b.adam_v,       b.rec,        b.bucket_cnt, b.bucket_off, b.triples,
-	                 b.rowrec,     b.rowtab,     c->target8_own, b.u8_lut,
+	                 b.rowrec,     b.rowtab,     b.rt_list, b.band_list, c->target8_own, b.u8_lut,
 	                 b.scan_sums,  b.vals[0],    b.vals[1],    b.cover, b.tile_range,
 	                 b.target,     b.image,  b.loss_partial, b.live_slots, b.stats, b.loss,  b.mse_ring,
 	                 b.state,      c->dstage, c->mbox,   b.tile_done, b.bucket_slots, c->peer_seq, c->touch_mem, c->reach_prev, c->reach_now, c->peer_traffic };
@@ -529,11 +529,13 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.rowtab, sizeof( unsigned ) * GS2D_ROWTAB_STRIDE * (size_t)std::max( g.n_total, 1 ) ) );
 	CKC( cudaMemset( b.rowtab, 0, sizeof( unsigned ) * GS2D_ROWTAB_STRIDE * (size_t)std::max( g.n_total, 1 ) ) );
 	CKC( cudaMemset( b.rowrec, 0xff, sizeof( RowRec ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.rt_list, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
+	CKC( cudaMalloc( &b.band_list, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
 	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
-	// [16-bit counters per (tile, slice) | 8-byte overflow counter of the slot binning | group rows: 32-bit arrival
+	// [16-bit counters per (tile, slice) | 8-byte overflow counter of the slot binning, 8-byte lengths of rt_list and band_list | group rows: 32-bit arrival
 	// counters per (group of 4 tiles, slice) | 16-bit totals per bucket in scan order] - the first two (three with group
 	// rows) are cleared by one memset per iteration (launch_preprocess_and_bin)
-	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + sizeof( unsigned long long ) +
+	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + 3 * sizeof( unsigned long long ) +
 	                                    sizeof( unsigned ) * (size_t)( g.nt_pad / 4 ) * g.n_slices +
 	                                    sizeof( unsigned short ) * ( n_buckets + 8 ) ) );
 	// slot rows: 16 bytes per (tile, slice) = group rows: 64 bytes per (group of 4 tiles, slice)

@@ -23,6 +23,8 @@
 #include "gs2d_internal.cuh"
 #include "gs2d_bins.cuh"
 
+#include <algorithm>
+
 #define PRE_THREADS 256
 
 // ------------------------------------------------------------------------------------------------ preprocess ---
@@ -56,6 +58,14 @@ struct PairOut
 	unsigned* grp_cnt;           // [nt_pad / 4][n_slices] arrivals of a (group, slice), also those that overflowed
 	unsigned* grp_rows;          // [nt_pad / 4][n_slices][GS2D_GROUP_SLOTS] keys (the memory of `slots`)
 	unsigned long long* ovf64;   // [nt_pad / 4][n_slices] four 16-bit counters: overflow arrivals per tile of the group
+	// A rank that owns a band of tile rows: the splats whose rows k_row_table has to solve (1 in 7 at 8 ranks) are
+	// appended here, so that its warps run with full lanes (nullptr: every splat is looked at, the single-GPU case)
+	unsigned* rt_list;
+	unsigned long long* rt_count;
+	// ... and the splats that passed the band test at all (k_band_filter): k_preprocess<.., LISTED> walks this list
+	// with full warps instead of finding 1 splat in 7 (8 ranks) in every warp
+	const unsigned* band_list;
+	const unsigned long long* band_count;
 };
 
 // Emit the pairs of tiles id_lo..id_hi (one tile row of one splat) at pos.., one 64-bit atomic per 4-tile group.
@@ -141,14 +151,23 @@ __device__ __forceinline__ void emit_row_groups( const Geometry& g, const PairOu
 // relaxed: write the record in the scaled form the relaxed-arithmetic blend kernels read (SplatRec, gs2d_internal.cuh)
 // rowtab: 1 = splats of at most GS2D_ROWTAB_STRIDE rows get their rows solved by k_row_table (else every
 // splat is left to the blend kernels' in-kernel solve: GS2D_ROWTAB=0, the A/B reference)
-template <int SLOTS>
+// LISTED: the splats are those of out.band_list (they passed k_band_filter's band test, which has also written the
+// touch bitmap and the reach masks); else every splat is looked at and tested here.
+template <int SLOTS, bool LISTED>
 __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, const float* __restrict__ params,
                                                                SplatRec* __restrict__ rec, RowRec* __restrict__ rowrec,
                                                                PairOut out, unsigned long long capacity, int cull,
                                                                int relaxed, int rowtab, unsigned* __restrict__ touch,
                                                                Buffers::Reach reach, DevState* __restrict__ st )
 {
-	const int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
+	int gi = blockIdx.x * PRE_THREADS + threadIdx.x;
+	if( LISTED )
+	{
+		const unsigned long long n_listed = *out.band_count;
+		if( (unsigned long long)blockIdx.x * PRE_THREADS >= n_listed )
+			return;
+		gi = (unsigned long long)gi < n_listed ? (int)out.band_list[gi] : g.n_total;
+	}
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	SplatBin sb;
 	sb.rtx0 = 1;
@@ -161,6 +180,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 	sb.k.begY = 1;
 	sb.k.endY = 0;
 	bool in_band = false; // passed the band test: the only splats that can receive a gradient on this rank
+	bool want_rt = false; // has rows for k_row_table to solve
 	unsigned reaches = 0; // sparse exchange: the ranks this splat can reach (computed for the quads this rank owns)
 	if( gi < g.n_total )
 	{
@@ -169,12 +189,12 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 		const float sx = params[PL_SX * g.n_pad + gi];
 		const float sy = params[PL_SY * g.n_pad + gi];
 		const float rot = params[PL_ROT * g.n_pad + gi];
-		if( reach.now && ( gi >> 2 ) >= reach.q0 && ( gi >> 2 ) < reach.q1 )
+		if( !LISTED && reach.now && ( gi >> 2 ) >= reach.q0 && ( gi >> 2 ) < reach.q1 )
 			reaches = reach_mask( py, sx, sy, reach.band_px, reach.n_ranks, reach.slack );
 
 		// a rank that owns a band of tile rows skips the splats that cannot reach it (band_rejects, gs2d_footprint.cuh)
 		// before the double sincos, the five IEEE divisions and the records, which only this rank's blend would read
-		const bool off_band = band_rejects( py, sx, sy, g.band_ty0 * GS2D_TILE, g.band_ty1 * GS2D_TILE );
+		const bool off_band = LISTED ? false : band_rejects( py, sx, sy, g.band_ty0 * GS2D_TILE, g.band_ty1 * GS2D_TILE );
 		in_band = !off_band;
 		if( off_band )
 			rowrec[gi].rows = ROWREC_NONE; // k_row_table looks at every splat
@@ -242,6 +262,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 				if( b0 <= b1 )
 					rr_rows = (unsigned)b0 | ( (unsigned)( b1 - b0 ) << 20 );
 			}
+			want_rt = rr_rows != ROWREC_NONE;
 			float4* rdst = reinterpret_cast<float4*>( rowrec + gi );
 			rdst[0] = make_float4( px, py, a, b );
 			rdst[1] = make_float4( d, __int_as_float( begY ), __int_as_float( endY ), __uint_as_float( rr_rows ) );
@@ -283,7 +304,7 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 			sb.k.endY = endY;
 		}
 	}
-	if( reach.now )
+	if( !LISTED && reach.now )
 	{
 		// OR over the four splats of the quad; the first lane of the quad stores the byte
 		unsigned m = reaches;
@@ -293,7 +314,20 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 		if( ( lane & 3 ) == 0 && q >= reach.q0 && q < reach.q1 )
 			reach.now[q] = (unsigned char)m;
 	}
-	if( touch )
+	if( out.rt_list )
+	{
+		const unsigned bal = __ballot_sync( 0xffffffffu, want_rt );
+		if( bal )
+		{
+			unsigned long long at = 0;
+			if( lane == 0 )
+				at = atomicAdd( out.rt_count, (unsigned long long)__popc( bal ) );
+			at = __shfl_sync( 0xffffffffu, at, 0 );
+			if( want_rt )
+				out.rt_list[at + __popc( bal & ( ( 1u << lane ) - 1u ) )] = (unsigned)gi;
+		}
+	}
+	if( !LISTED && touch )
 	{
 		// sparse gradient exchange (PeerPtrs::touch): one bit per quad of 4 consecutive splats, the 8 quads of a warp
 		// are 8 aligned bits of one word
@@ -335,6 +369,30 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 	const unsigned R = __shfl_sync( 0xffffffffu, rows_incl, 31 );
 	__syncwarp();
 
+	if constexpr( SLOTS == 2 )
+	{
+		// Group rows need no place in the pair list, so there is nothing to reserve and nothing to stash: span and
+		// emission in one pass. (The number of pairs - DevState::n_keys, the capacity check - comes out of the scan of
+		// the bucket totals, k_scan_sums; the per-chunk atomicAdd on that one counter was what a block waited for.)
+		for( unsigned item = lane; item < R; item += 32 )
+		{
+			unsigned owner = 0;
+#pragma unroll
+			for( int step = 16; step > 0; step >>= 1 )
+				if( wrows[owner + step - 1] <= item )
+					owner += step;
+			const SplatBin& o = wbin[owner];
+			const unsigned first = owner ? wrows[owner - 1] : 0u;
+			const int ty = o.ty0 + (int)( item - first );
+			int lo, hi;
+			if( tile_span( o.k, ty, g.H, o.rtx0, o.rtx1, lo, hi ) )
+			{
+				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
+				emit_row_groups( g, out, row + (unsigned)lo, row + (unsigned)hi, o.slice, (unsigned)o.local, capacity, cull >> 8 );
+			}
+		}
+		return;
+	}
 	for( unsigned chunk = 0; chunk < R; chunk += ITEMS_PER_CHUNK )
 	{
 		const unsigned n_items = min( (unsigned)ITEMS_PER_CHUNK, R - chunk );
@@ -391,15 +449,86 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 				const int ty = o.ty0 + (int)( item - first );
 				const unsigned lo = span & 0xfffu, hi = ( span >> 12 ) & 0xfffu;
 				const unsigned row = (unsigned)( o.tile_base + ty * g.tiles_x );
-				if constexpr( SLOTS == 2 )
-					emit_row_groups( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, capacity, cull >> 8 );
-				else
-					emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
+				emit_row<SLOTS>( g, out, row + lo, row + hi, o.slice, (unsigned)o.local, pos, capacity );
 				pos += hi - lo + 1u;
 			}
 		}
 		__syncwarp();
 	}
+}
+
+// ---------------------------------------------------------------------------------------------- band filter ---
+// A rank that owns a band of tile rows (N ranks): the band test of every splat, streamed - three parameters per
+// splat - with what hangs on it: the reach masks of the quads this rank owns and the touch bitmap of the sparse
+// exchange (PeerPtrs), and the list of the splats that passed, which k_preprocess<.., LISTED> then walks with full
+// warps. In k_preprocess itself 1 splat in 7 passes at 8 ranks, so that nearly every warp ran the double-precision
+// sincos, the divisions and the record stores for four or five lanes.
+#define FILTER_THREADS 1024
+__global__ void __launch_bounds__( FILTER_THREADS ) k_band_filter( Geometry g, const float* __restrict__ params,
+                                                                   RowRec* __restrict__ rowrec, int mark_rowrec,
+                                                                   unsigned* __restrict__ touch, Buffers::Reach reach,
+                                                                   unsigned* __restrict__ band_list,
+                                                                   unsigned long long* __restrict__ band_count )
+{
+	const int gi = blockIdx.x * FILTER_THREADS + threadIdx.x;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	bool in_band = false;
+	unsigned reaches = 0;
+	if( gi < g.n_total )
+	{
+		const float py = params[PL_PY * g.n_pad + gi];
+		const float sx = params[PL_SX * g.n_pad + gi];
+		const float sy = params[PL_SY * g.n_pad + gi];
+		if( reach.now && ( gi >> 2 ) >= reach.q0 && ( gi >> 2 ) < reach.q1 )
+			reaches = reach_mask( py, sx, sy, reach.band_px, reach.n_ranks, reach.slack );
+		in_band = !band_rejects( py, sx, sy, g.band_ty0 * GS2D_TILE, g.band_ty1 * GS2D_TILE );
+		if( !in_band && mark_rowrec )
+			rowrec[gi].rows = ROWREC_NONE; // k_row_table without its list looks at every splat
+	}
+	if( reach.now )
+	{
+		unsigned m = reaches;
+		m |= __shfl_xor_sync( 0xffffffffu, m, 1 );
+		m |= __shfl_xor_sync( 0xffffffffu, m, 2 );
+		const int q = gi >> 2;
+		if( ( lane & 3 ) == 0 && q >= reach.q0 && q < reach.q1 )
+			reach.now[q] = (unsigned char)m;
+	}
+	const unsigned bal = __ballot_sync( 0xffffffffu, in_band );
+	if( touch && lane == 0 && bal )
+	{
+		// one bit per quad of 4 consecutive splats, the 8 quads of a warp are 8 aligned bits of one word
+		unsigned bits = 0;
+#pragma unroll
+		for( int qd = 0; qd < 8; qd++ )
+			bits |= ( ( bal >> ( 4 * qd ) ) & 0xfu ) ? ( 1u << qd ) : 0u;
+		const unsigned q = (unsigned)gi >> 2; // first quad of the warp: a multiple of 8
+		atomicOr( touch + ( q >> 5 ), bits << ( q & 31u ) );
+	}
+	// one reservation of the list per block (a reservation per warp is 31 000 returning atomics on one address)
+	__shared__ unsigned wcount[FILTER_THREADS / 32];
+	__shared__ unsigned long long block_at;
+	if( lane == 0 )
+		wcount[warp] = (unsigned)__popc( bal );
+	__syncthreads();
+	if( warp == 0 )
+	{
+		const unsigned mine = wcount[lane];
+		unsigned incl = mine;
+#pragma unroll
+		for( int o = 1; o < 32; o <<= 1 )
+		{
+			const unsigned v = __shfl_up_sync( 0xffffffffu, incl, o );
+			if( lane >= o )
+				incl += v;
+		}
+		wcount[lane] = incl - mine;
+		if( lane == 31 )
+			block_at = incl ? atomicAdd( band_count, (unsigned long long)incl ) : 0ull;
+	}
+	__syncthreads();
+	if( in_band )
+		band_list[block_at + wcount[warp] + __popc( bal & ( ( 1u << lane ) - 1u ) )] = (unsigned)gi;
 }
 
 // ---------------------------------------------------------------------------------------------- row table ---
@@ -419,32 +548,38 @@ __global__ void __launch_bounds__( PRE_THREADS, 6 ) k_preprocess( Geometry g, co
 // per scheduler the solve's dependent chain (sqrt, two divisions) finds no more free slots than it does alone. Two
 // kernels on two streams do not overlap either (the first kernel's blocks hold the SMs).
 #define ROWTAB_LANES 8
+// rt_list / rt_count: the splats to solve (k_preprocess appended them; a rank's band) - a grid-stride loop over the
+// list; nullptr: every splat, one group of lanes each.
 __global__ void __launch_bounds__( 256 ) k_row_table( Geometry g, const RowRec* __restrict__ rowrec,
-                                                      unsigned* __restrict__ rowtab )
+                                                      unsigned* __restrict__ rowtab,
+                                                      const unsigned* __restrict__ rt_list,
+                                                      const unsigned long long* __restrict__ rt_count )
 {
-	const unsigned t = blockIdx.x * 256u + threadIdx.x;
-	const unsigned gi = t / ROWTAB_LANES, sub = t % ROWTAB_LANES;
-	if( gi >= (unsigned)g.n_total )
-		return;
-	const float4* rr = reinterpret_cast<const float4*>( rowrec + gi );
-	const float4 q1 = __ldg( rr + 1 ); // d begY endY rows
-	const unsigned rows = (unsigned)__float_as_int( q1.w );
-	if( rows == ROWREC_NONE )
-		return;
-	const float4 q0 = __ldg( rr );     // px py a b
-	// [y0, y1] lies inside [begY, endY] and inside the image (k_preprocess), so the row tests of row_span are void
-	const int y0 = (int)( rows & 0xfffffu ), y1 = y0 + (int)( rows >> 20 );
-	const float px = q0.x, py = q0.y, a = q0.z, b = q0.w, d = q1.x;
-	const float a4 = xmul( 4.0f, a ), b2 = xmul( 2.0f, b );
-	const bool a_ok = far_from_the_edges( a );
-	const float ra = rcp_refined( a );
-	unsigned* tab = rowtab + (size_t)gi * GS2D_ROWTAB_STRIDE;
-#pragma unroll 1
-	for( int y = y0 + (int)sub; y <= y1; y += ROWTAB_LANES )
+	const unsigned n = rt_list ? (unsigned)*rt_count : (unsigned)g.n_total;
+	for( unsigned t = blockIdx.x * 256u + threadIdx.x; t < n * ROWTAB_LANES; t += gridDim.x * 256u )
 	{
-		int begX = 0, endX = 0;
-		const bool any = row_span_dense( px, py, a, b, d, a4, b2, ra, a_ok, y, begX, endX );
-		tab[y & ( GS2D_ROWTAB_STRIDE - 1 )] = pack_row_span( any, begX, endX, g.W );
+		const unsigned sub = t % ROWTAB_LANES;
+		const unsigned gi = rt_list ? rt_list[t / ROWTAB_LANES] : t / ROWTAB_LANES;
+		const float4* rr = reinterpret_cast<const float4*>( rowrec + gi );
+		const float4 q1 = __ldg( rr + 1 ); // d begY endY rows
+		const unsigned rows = (unsigned)__float_as_int( q1.w );
+		if( rows == ROWREC_NONE )
+			continue;
+		const float4 q0 = __ldg( rr );     // px py a b
+		// [y0, y1] lies inside [begY, endY] and inside the image (k_preprocess), so the row tests of row_span are void
+		const int y0 = (int)( rows & 0xfffffu ), y1 = y0 + (int)( rows >> 20 );
+		const float px = q0.x, py = q0.y, a = q0.z, b = q0.w, d = q1.x;
+		const float a4 = xmul( 4.0f, a ), b2 = xmul( 2.0f, b );
+		const bool a_ok = far_from_the_edges( a );
+		const float ra = rcp_refined( a );
+		unsigned* tab = rowtab + (size_t)gi * GS2D_ROWTAB_STRIDE;
+#pragma unroll 1
+		for( int y = y0 + (int)sub; y <= y1; y += ROWTAB_LANES )
+		{
+			int begX = 0, endX = 0;
+			const bool any = row_span_dense( px, py, a, b, d, a4, b2, ra, a_ok, y, begX, endX );
+			tab[y & ( GS2D_ROWTAB_STRIDE - 1 )] = pack_row_span( any, begX, endX, g.W );
+		}
 	}
 }
 
@@ -509,8 +644,10 @@ __global__ void __launch_bounds__( SCAN_THREADS ) k_scan_local( Geometry g, cons
 		sums[blockIdx.x] = tot;
 }
 // one block: exclusive scan of the block totals; the capacity check of the iteration
+// total_is_keys (group rows): k_preprocess has not counted the pairs; their number is the grand total of the scan
 __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ sums, unsigned nb,
-                                                       unsigned long long capacity, DevState* __restrict__ st )
+                                                       unsigned long long capacity, DevState* __restrict__ st,
+                                                       int total_is_keys )
 {
 	__shared__ unsigned wtot[32];
 	__shared__ unsigned carry_s;
@@ -551,6 +688,11 @@ __global__ void __launch_bounds__( 1024 ) k_scan_sums( unsigned* __restrict__ su
 		if( threadIdx.x == 0 )
 			carry_s = carry + tot;
 		__syncthreads();
+	}
+	if( total_is_keys && threadIdx.x == 0 )
+	{
+		st->n_keys = carry_s;
+		st->need_capacity = ( carry_s > capacity ) ? carry_s : 0ull;
 	}
 }
 // The block-local offsets are not patched in a third pass: the consumers add the scanned block total themselves
@@ -927,28 +1069,57 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	// the overflow counter sits behind the bucket counters and is cleared with them; behind it the arrival counters
 	// of the group rows (cleared too when they are in use) and the totals in scan order (every one is written)
 	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + n_cnt16 );
-	po.grp_cnt = reinterpret_cast<unsigned*>( po.n_over + 1 );
+	po.grp_cnt = reinterpret_cast<unsigned*>( po.n_over + 3 ); // n_over, rt_count, band_count
 	po.grp_rows = reinterpret_cast<unsigned*>( b.bucket_slots );
 	po.ovf64 = po.cnt64;
 	unsigned short* tot16 = reinterpret_cast<unsigned short*>( po.grp_cnt + n_pairs_all );
+	// a rank with a band (not the whole image): k_row_table works from the list of the splats that have rows in it
+	const bool banded = g.band_ty0 > 0 || g.band_ty1 < g.tiles_y;
+	po.rt_count = po.n_over + 1;
+	po.rt_list = banded && b.rt_list && gs2d_tune( "GS2D_RT_LIST", 1 ) ? b.rt_list : nullptr;
+	const bool listed = banded && b.band_list && gs2d_tune( "GS2D_BAND_LIST", 1 );
+	po.band_list = b.band_list;
+	po.band_count = po.n_over + 2;
 	cudaMemsetAsync( b.bucket_cnt, 0,
-	                 sizeof( unsigned short ) * n_cnt16 + sizeof( unsigned long long ) +
+	                 sizeof( unsigned short ) * n_cnt16 + 3 * sizeof( unsigned long long ) +
 	                     ( mode == 2 ? sizeof( unsigned ) * n_pairs_all : 0 ),
 	                 s );
 	if( b.touch )
 		cudaMemsetAsync( b.touch, 0, sizeof( unsigned ) * ( (size_t)g.n_pad / 128 + 1 ), s );
 	const int nb = ( g.n_total + PRE_THREADS - 1 ) / PRE_THREADS;
 	const int relaxed = gs2d_exact_mode() ? 0 : 1, rowtab = gs2d_tune( "GS2D_ROWTAB", 1 ) ? 1 : 0;
+	const int cull = gs2d_tune( "GS2D_CULL", 1 ) | ( gs2d_tune( "GS2D_K1_PROBE", 0 ) << 8 );
+	if( listed )
+	{
+		k_band_filter<<<( g.n_total + FILTER_THREADS - 1 ) / FILTER_THREADS, FILTER_THREADS, 0, s>>>(
+		    g, b.params, b.rowrec, po.rt_list ? 0 : 1, b.touch, b.reach, b.band_list, po.n_over + 2 );
+		launches += 1;
+	}
+#define K1( MODE, LISTED )                                                                                            \
+	k_preprocess<MODE, LISTED><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, cull, relaxed,  \
+	                                                       rowtab, b.touch, b.reach, b.state )
 	if( mode == 2 )
-		k_preprocess<2><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity,
-		                                            gs2d_tune( "GS2D_CULL", 1 ) | ( gs2d_tune( "GS2D_K1_PROBE", 0 ) << 8 ),
-		                                            relaxed, rowtab, b.touch, b.reach, b.state );
+	{
+		if( listed )
+			K1( 2, true );
+		else
+			K1( 2, false );
+	}
 	else if( slots )
-		k_preprocess<1><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                            relaxed, rowtab, b.touch, b.reach, b.state );
+	{
+		if( listed )
+			K1( 1, true );
+		else
+			K1( 1, false );
+	}
 	else
-		k_preprocess<0><<<nb, PRE_THREADS, 0, s>>>( g, b.params, b.rec, b.rowrec, po, b.capacity, gs2d_tune( "GS2D_CULL", 1 ),
-		                                            relaxed, rowtab, b.touch, b.reach, b.state );
+	{
+		if( listed )
+			K1( 0, true );
+		else
+			K1( 0, false );
+	}
+#undef K1
 	launches += 1;
 	if( after_emit )
 		cudaEventRecord( after_emit, s );
@@ -966,7 +1137,10 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 			rs = side->stream;
 			forked = true;
 		}
-		k_row_table<<<rt_blocks, 256, 0, rs>>>( g, b.rowrec, b.rowtab );
+		if( po.rt_list ) // persistent grid over the list
+			k_row_table<<<std::min( rt_blocks, 148u * 8u ), 256, 0, rs>>>( g, b.rowrec, b.rowtab, po.rt_list, po.rt_count );
+		else
+			k_row_table<<<rt_blocks, 256, 0, rs>>>( g, b.rowrec, b.rowtab, nullptr, nullptr );
 		launches += 1;
 		if( forked )
 			cudaEventRecord( side->ev_join, rs );
@@ -999,7 +1173,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		const unsigned scan_nb = ( hi - lo + 1u + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
 		k_group_count<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, tot16, win );
 		k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, tot16, b.bucket_off, lo, hi, hi + 1u, b.scan_sums );
-		k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
+		k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state, 1 );
 		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over, 1 );
 		k_rank_groups<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, b.bucket_off, b.scan_sums, b.vals[1],
 		                                       b.vals[0], b.tile_range, lo, win, b.state );
@@ -1009,7 +1183,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	}
 	const unsigned scan_nb = ( hi - lo + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
 	k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, nullptr, b.bucket_off, lo, hi, hi, b.scan_sums );
-	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state );
+	k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state, 0 );
 	if( slots )
 	{
 		// few triples, if any: a small grid (the kernel is a grid-stride loop over *n_over)

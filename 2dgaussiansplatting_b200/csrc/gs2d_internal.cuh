@@ -150,6 +150,8 @@ struct Buffers
 	SplatRec* rec;  // [n_total]
 	RowRec* rowrec; // [n_total]
 	unsigned* rowtab; // [n_total][GS2D_ROWTAB_STRIDE] packed row spans (k_row_table -> k_forward)
+	unsigned* rt_list; // [n_total] a banded rank: the splats k_row_table has to solve this iteration (k_preprocess appends)
+	unsigned* band_list; // [n_total] a banded rank: the splats that passed the band test (k_band_filter appends)
 	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
 	unsigned short* bucket_slots; // [n_slices][nt_pad][GS2D_BUCKET_SLOTS] first arrivals of every bucket (slot binning)
 	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
