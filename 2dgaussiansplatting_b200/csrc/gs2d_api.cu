@@ -532,10 +532,11 @@ extern "C" int gs2d_create( gs2d_ctx** out, int W, int H, int n_splats, int n_im
 	CKC( cudaMalloc( &b.rt_list, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
 	CKC( cudaMalloc( &b.band_list, sizeof( unsigned ) * (size_t)std::max( g.n_total, 1 ) ) );
 	const size_t n_buckets = (size_t)g.n_tiles_total * g.n_slices;
-	// [16-bit counters per (tile, slice) | 8-byte overflow counter of the slot binning, 8-byte lengths of rt_list and band_list | group rows: 32-bit arrival
+	// [16-bit counters per (tile, slice) | 8-byte overflow counter of the slot binning, 8-byte lengths of rt_list and band_list, ticket and status words of the scan's look-back | group rows: 32-bit arrival
 	// counters per (group of 4 tiles, slice) | 16-bit totals per bucket in scan order] - the first two (three with group
 	// rows) are cleared by one memset per iteration (launch_preprocess_and_bin)
-	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices + 3 * sizeof( unsigned long long ) +
+	CKC( cudaMalloc( &b.bucket_cnt, sizeof( unsigned short ) * (size_t)g.nt_pad * g.n_slices +
+	                                    ( 4 + n_buckets / 1024 + 4 ) * sizeof( unsigned long long ) +
 	                                    sizeof( unsigned ) * (size_t)( g.nt_pad / 4 ) * g.n_slices +
 	                                    sizeof( unsigned short ) * ( n_buckets + 8 ) ) );
 	// slot rows: 16 bytes per (tile, slice) = group rows: 64 bytes per (group of 4 tiles, slice)

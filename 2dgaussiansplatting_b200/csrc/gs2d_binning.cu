@@ -930,6 +930,148 @@ __global__ void __launch_bounds__( 256 ) k_group_count( Geometry g, const unsign
 	}
 }
 
+// k_group_count + k_scan_local + k_scan_sums in ONE kernel (n_slices <= 256: a block of 256 (group, slice) pairs is
+// 256 / n_slices whole groups = 1024 consecutive buckets of the scan order). Every thread counts the entries of the
+// four buckets of its pair straight from the group row; the counts change places through shared memory (pair order ->
+// scan order), the block scans them, and the block totals are chained by a decoupled look-back (each block publishes
+// its total, then its inclusive prefix, in one 64-bit status word; a block adds up the totals of its predecessors
+// until it meets an inclusive prefix). Blocks take their place in the chain from a ticket counter, so a block's
+// predecessors have always started. Same outputs as the three kernels: block-local offsets + sums[block]; the last
+// block writes the number of pairs and the capacity verdict.
+#define SCAN_FLAG_AGG ( 1ull << 62 )
+#define SCAN_FLAG_INC ( 2ull << 62 )
+#define SCAN_VALUE_MASK ( ( 1ull << 62 ) - 1ull )
+__global__ void __launch_bounds__( 256 ) k_group_scan( Geometry g, const unsigned* __restrict__ grp_cnt,
+                                                       const unsigned* __restrict__ rows,
+                                                       const unsigned long long* __restrict__ ovf64,
+                                                       unsigned* __restrict__ offset, unsigned* __restrict__ sums,
+                                                       unsigned long long* __restrict__ ticket,
+                                                       unsigned long long* __restrict__ status, GroupWindow win,
+                                                       unsigned n_blocks, unsigned n_off,
+                                                       unsigned long long capacity, DevState* __restrict__ st )
+{
+	__shared__ unsigned short cnt_s[SCAN_PER_BLOCK];
+	__shared__ unsigned wtot[8];
+	__shared__ unsigned blk_s;
+	if( threadIdx.x == 0 )
+		blk_s = (unsigned)atomicAdd( ticket, 1ull );
+	__syncthreads();
+	const unsigned blk = blk_s;
+	const unsigned ns = (unsigned)g.n_slices;
+	const unsigned p = blk * 256u + threadIdx.x;
+	const bool valid = p < win.n_pairs;
+	const size_t pair = (size_t)win.grp_lo * ns + ( valid ? p : 0u );
+	const unsigned grp = (unsigned)( pair / ns ), slice = (unsigned)( pair - (size_t)grp * ns );
+	{
+		const unsigned c_raw = valid ? grp_cnt[pair] : 0u, c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
+		unsigned w[GS2D_GROUP_SLOTS], n[4];
+		load_row( w, rows, pair, c );
+		group_counts( w, c, __reduce_max_sync( 0xffffffffu, c ), n );
+		if( c_raw > (unsigned)GS2D_GROUP_SLOTS )
+		{
+			const unsigned long long ov = ovf64[pair];
+#pragma unroll
+			for( unsigned f = 0; f < 4u; f++ )
+				n[f] += (unsigned)( ov >> ( 16u * f ) ) & 0xffffu;
+		}
+		// pair order -> scan order: bucket (tile, slice) of the block is item (tile - first tile of the block) * ns + slice
+		// (from the thread index: a thread beyond the window's pairs still clears its four items)
+		const unsigned g_local = threadIdx.x / ns, s_local = threadIdx.x - g_local * ns;
+#pragma unroll
+		for( unsigned f = 0; f < 4u; f++ )
+		{
+			const unsigned tile = grp * 4u + f;
+			const bool in = valid && tile >= win.tile_lo && tile < win.tile_hi;
+			cnt_s[( g_local * 4u + f ) * ns + s_local] = (unsigned short)( in ? n[f] : 0u );
+		}
+	}
+	__syncthreads();
+	// block-local exclusive scan of the 1024 items, four per thread (as k_scan_local)
+	const unsigned base = win.grp_lo * 4u * ns; // first bucket of block 0
+	const unsigned i0 = base + blk * SCAN_PER_BLOCK + threadIdx.x * 4u;
+	unsigned v[4];
+#pragma unroll
+	for( int k = 0; k < 4; k++ )
+		v[k] = cnt_s[threadIdx.x * 4u + k];
+	const unsigned tsum = v[0] + v[1] + v[2] + v[3];
+	unsigned incl = tsum;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+	for( int o = 1; o < 32; o <<= 1 )
+	{
+		const unsigned t = __shfl_up_sync( 0xffffffffu, incl, o );
+		if( lane >= o )
+			incl += t;
+	}
+	if( lane == 31 )
+		wtot[warp] = incl;
+	__syncthreads();
+	unsigned wb = 0, tot = 0;
+#pragma unroll
+	for( int w = 0; w < 8; w++ )
+	{
+		const unsigned t = wtot[w];
+		if( w < warp )
+			wb += t;
+		tot += t;
+	}
+	unsigned run = wb + incl - tsum;
+#pragma unroll
+	for( int k = 0; k < 4; k++ )
+	{
+		if( i0 + k < n_off )
+			offset[i0 + k] = run;
+		run += v[k];
+	}
+	// chain of the block totals: the first warp looks back 32 predecessors at a time
+	if( warp == 0 )
+	{
+		if( lane == 0 && blk > 0u )
+			asm volatile( "st.release.gpu.global.u64 [%0], %1;" ::"l"( status + blk ), "l"( SCAN_FLAG_AGG | (unsigned long long)tot ) : "memory" );
+		unsigned long long prefix = 0;
+		for( int j = (int)blk - 1; j >= 0; j -= 32 )
+		{
+			const int idx = j - lane;
+			unsigned long long sv = SCAN_FLAG_INC; // in front of block 0: an inclusive prefix of 0
+			if( idx >= 0 )
+			{
+				unsigned spin = 0;
+				do
+				{
+					asm volatile( "ld.acquire.gpu.global.u64 %0, [%1];" : "=l"( sv ) : "l"( status + idx ) : "memory" );
+					if( sv == 0ull )
+					{
+						__nanosleep( 64 ); // leave the issue slots and the L2 to the blocks that are still counting
+						if( ++spin > ( 1u << 22 ) )
+						{
+							st->peer_fault = 3; // cannot happen (ticket order); never hang the device
+							sv = SCAN_FLAG_INC;
+						}
+					}
+				} while( sv == 0ull );
+			}
+			// the nearest predecessor with an inclusive prefix ends the walk; the totals of the blocks in front of it count
+			const unsigned inc = __ballot_sync( 0xffffffffu, ( sv & SCAN_FLAG_INC ) != 0ull );
+			const unsigned upto = inc ? (unsigned)__ffs( inc ) - 1u : 31u;
+			const unsigned mine = (unsigned)lane <= upto ? (unsigned)( sv & 0xffffffffull ) : 0u; // totals fit 32 bits (offsets are)
+			prefix += __reduce_add_sync( 0xffffffffu, mine );
+			if( inc )
+				break;
+		}
+		if( lane == 0 )
+		{
+			asm volatile( "st.release.gpu.global.u64 [%0], %1;" ::"l"( status + blk ), "l"( SCAN_FLAG_INC | ( prefix + tot ) ) : "memory" );
+			sums[blk] = (unsigned)prefix;
+			if( blk == n_blocks - 1u )
+			{
+				const unsigned long long total = prefix + tot;
+				st->n_keys = total;
+				st->need_capacity = ( total > capacity ) ? total : 0ull;
+			}
+		}
+	}
+}
+
 // The lists of the four tiles of a group, ordered by splat index: sort the row's keys once, deal them to the tiles
 // they cover (gs2d_bins.cuh). A bucket with overflow arrivals (k_place put them at its end) is joined in the
 // unordered list and ranked by counting, like the sort-free path does for every long bucket.
@@ -1069,7 +1211,10 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	// the overflow counter sits behind the bucket counters and is cleared with them; behind it the arrival counters
 	// of the group rows (cleared too when they are in use) and the totals in scan order (every one is written)
 	po.n_over = reinterpret_cast<unsigned long long*>( b.bucket_cnt + n_cnt16 );
-	po.grp_cnt = reinterpret_cast<unsigned*>( po.n_over + 3 ); // n_over, rt_count, band_count
+	// n_over, rt_count, band_count, then the ticket counter and the status words of k_group_scan's look-back
+	unsigned long long* scan_ticket = po.n_over + 3;
+	const size_t n_status = (size_t)g.n_tiles_total * g.n_slices / SCAN_PER_BLOCK + 4;
+	po.grp_cnt = reinterpret_cast<unsigned*>( scan_ticket + 1 + n_status );
 	po.grp_rows = reinterpret_cast<unsigned*>( b.bucket_slots );
 	po.ovf64 = po.cnt64;
 	unsigned short* tot16 = reinterpret_cast<unsigned short*>( po.grp_cnt + n_pairs_all );
@@ -1081,7 +1226,7 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	po.band_list = b.band_list;
 	po.band_count = po.n_over + 2;
 	cudaMemsetAsync( b.bucket_cnt, 0,
-	                 sizeof( unsigned short ) * n_cnt16 + 3 * sizeof( unsigned long long ) +
+	                 sizeof( unsigned short ) * n_cnt16 + ( 4 + n_status ) * sizeof( unsigned long long ) +
 	                     ( mode == 2 ? sizeof( unsigned ) * n_pairs_all : 0 ),
 	                 s );
 	if( b.touch )
@@ -1169,15 +1314,30 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 		win.grp_lo = win.tile_lo >> 2;
 		win.n_pairs = ( ( ( win.tile_hi + 3u ) >> 2 ) - win.grp_lo ) * (unsigned)g.n_slices;
 		const unsigned pair_nb = ( win.n_pairs + 255u ) / 256u;
-		// one more scan item than buckets: the end of the window's last bucket
-		const unsigned scan_nb = ( hi - lo + 1u + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
-		k_group_count<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, tot16, win );
-		k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, tot16, b.bucket_off, lo, hi, hi + 1u, b.scan_sums );
-		k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state, 1 );
-		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, lo, b.vals[1], b.state, po.n_over, 1 );
+		unsigned scan_base = lo;
+		if( g.n_slices <= 256 && gs2d_tune( "GS2D_SCAN_FUSED", 1 ) )
+		{
+			// one kernel: counts from the group rows, block scan, block totals chained by look-back. Its blocks are whole
+			// groups, so its first bucket is the first bucket of the window's first GROUP; one more scan item than
+			// buckets (the end of the window's last bucket)
+			scan_base = win.grp_lo * 4u * (unsigned)g.n_slices;
+			const unsigned scan_nb = ( hi - scan_base + 1u + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+			k_group_scan<<<scan_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, b.bucket_off, b.scan_sums, scan_ticket,
+			                                      scan_ticket + 1, win, scan_nb, hi + 1u, b.capacity, b.state );
+			launches += 1;
+		}
+		else
+		{
+			const unsigned scan_nb = ( hi - lo + 1u + SCAN_PER_BLOCK - 1 ) / SCAN_PER_BLOCK;
+			k_group_count<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, tot16, win );
+			k_scan_local<<<scan_nb, SCAN_THREADS, 0, s>>>( g, b.bucket_cnt, tot16, b.bucket_off, lo, hi, hi + 1u, b.scan_sums );
+			k_scan_sums<<<1, 1024, 0, s>>>( b.scan_sums, scan_nb, b.capacity, b.state, 1 );
+			launches += 3;
+		}
+		k_place<<<148, 256, 0, s>>>( g, b.triples, b.bucket_off, b.scan_sums, scan_base, b.vals[1], b.state, po.n_over, 1 );
 		k_rank_groups<<<pair_nb, 256, 0, s>>>( g, po.grp_cnt, po.grp_rows, po.ovf64, b.bucket_off, b.scan_sums, b.vals[1],
-		                                       b.vals[0], b.tile_range, lo, win, b.state );
-		launches += 5;
+		                                       b.vals[0], b.tile_range, scan_base, win, b.state );
+		launches += 2;
 		join();
 		return launches;
 	}
