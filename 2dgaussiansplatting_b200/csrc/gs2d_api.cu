@@ -330,7 +330,8 @@ static int alloc_keys( gs2d_ctx* c, unsigned long long capacity )
 	CK( cudaMalloc( &b.triples, sizeof( unsigned long long ) * capacity ) );
 	CK( cudaMalloc( &b.vals[0], sizeof( unsigned ) * capacity ) );
 	CK( cudaMalloc( &b.vals[1], sizeof( unsigned ) * capacity ) );
-	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * 8 * capacity ) );
+	// coverage words, and behind them one word per round of a tile (round_vis_index, gs2d_blend.cuh)
+	CK( cudaMalloc( &b.cover, sizeof( unsigned ) * ( 8 * capacity + capacity / 32 + (size_t)c->g.n_tiles_total + 8 ) ) );
 	b.capacity = capacity;
 	return GS2D_OK;
 }

@@ -114,7 +114,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
                                                               float* __restrict__ grads,
                                                               unsigned long long* __restrict__ live_slots,
                                                               const DevState* __restrict__ st,
-                                                              const unsigned* tile_done )
+                                                              const unsigned* tile_done,
+                                                              const unsigned* __restrict__ round_vis )
 {
 	if( st->need_capacity )
 	{
@@ -205,6 +206,12 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		cp_async_commit();
 	}
 	unsigned idx_nxt = ( start + GS2D_BATCH + lane < end ) ? vals[start + GS2D_BATCH + lane] : 0u;
+	// The entries of a round that blended into a pixel in the forward pass (k_forward left one mask per round): the
+	// two passes evaluate the same alpha and transmittance chain bit for bit, so these are exactly the entries that
+	// would pass a test against this pass's live masks - 20 instructions per popped entry that are not spent here.
+	// The mask of the next round is requested a round ahead (through L2: the forward grid may still be running).
+	unsigned rvi = ( start >> 5 ) + tile_id; // round_vis_index( start, tile_id, base ), advanced round by round
+	unsigned ent_nxt = __ldcg( round_vis + rvi );
 
 	int stage = 0;
 	for( unsigned base = start; base < end; base += GS2D_BATCH, stage ^= 1 )
@@ -212,6 +219,10 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		const int nb = min( (unsigned)GS2D_BATCH, end - base );
 		const unsigned nbase = base + GS2D_BATCH;
 		const unsigned idx_this = idx_cur;
+		unsigned ent = ent_nxt;
+		rvi++;
+		if( nbase < end )
+			ent_nxt = __ldcg( round_vis + rvi ); // (a round the forward pass never reached: unwritten, and never used here either)
 		if( nbase < end )
 		{
 			gather_record<4>( sm, stage ^ 1, lane, rec, idx_nxt, nbase + lane < end );
@@ -224,14 +235,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 		else
 			cp_async_wait<0>();
 		__syncwarp();
-		uint4 cwa, cwb;
-		touching_entries( sm, stage, nb, lane, cwa, cwb );
-		// entries that cover a pixel that is live now (lane k tests entry k), as in k_forward
-		unsigned ent = __ballot_sync( 0xffffffffu, ( ( cwa.x & live[0] ) | ( cwa.y & live[1] ) | ( cwa.z & live[2] ) |
-		                                             ( cwa.w & live[3] ) | ( cwb.x & live[4] ) | ( cwb.y & live[5] ) |
-		                                             ( cwb.z & live[6] ) | ( cwb.w & live[7] ) ) != 0u );
-
-		unsigned visited = 0;
+		const unsigned visited = ent;
 		unsigned grp_n = 0u, grp_k = 0u; // visited entries parked in stage4, their list positions (8 bits each)
 #pragma unroll 1
 		while( ent )
@@ -241,13 +245,6 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[stage][k][0] );
 			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[stage][k][4] );
 			const unsigned wd[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
-			unsigned hit = 0;
-#pragma unroll
-			for( int j = 0; j < 8; j++ )
-				hit |= wd[j] & live[j];
-			if( hit == 0u )
-				continue;
-			visited |= 1u << k;
 			const SplatRec& s = sm.rec[stage][k];
 			const float4 q0 = *reinterpret_cast<const float4*>( &s.px ); // px py B D
 			const float4 q1 = *reinterpret_cast<const float4*>( &s.A );  // A cr cg cb
@@ -435,7 +432,8 @@ static void launch_backward_as( dim3 grid, const Geometry& g, const Buffers& b, 
 	                    (const uint2*)b.tile_range,
 	                    g.target_u8 ? reinterpret_cast<const float4*>( b.target8 ) : (const float4*)b.target, (const float4*)b.image,
 	                    (const unsigned*)b.cover, b.grads, slots, (const DevState*)b.state,
-	                    (const unsigned*)( PDL ? b.tile_done : nullptr ) );
+	                    (const unsigned*)( PDL ? b.tile_done : nullptr ),
+	                    (const unsigned*)( b.cover + 8 * (size_t)b.capacity ) );
 }
 template <int MINB, bool PDL, bool COUNT>
 static void launch_backward_minb( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, bool with_opacity,

@@ -151,6 +151,15 @@ __device__ __forceinline__ bool pdl_wait_tile( const unsigned* flag, int lane )
 	return ok != 0u;
 }
 
+// Where the forward pass leaves the 32-bit mask of a round's entries that blended into a pixel (k_forward -> k_backward):
+// one word per round of a tile. Rounds of tile t number (start_t >> 5) + t + round: floor((s + n)/32) >=
+// floor(s/32) + ceil(n/32) - 1, so the words of consecutive tiles never meet; capacity/32 + n_tiles + 1 words in all,
+// kept behind the coverage words (Buffers::cover).
+__device__ __forceinline__ size_t round_vis_index( unsigned start, unsigned tile_id, unsigned base )
+{
+	return (size_t)( start >> 5 ) + tile_id + ( ( base - start ) >> 5 );
+}
+
 // WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)
 template <int WSTAGES>
 struct TileSmem

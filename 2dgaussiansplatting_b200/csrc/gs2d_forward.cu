@@ -45,7 +45,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
                                                              const DevState* __restrict__ st, int visit_hist,
                                                              unsigned* __restrict__ tile_done,
                                                              const unsigned* __restrict__ rowtab,
-                                                             const RowRec* __restrict__ rowrec )
+                                                             const RowRec* __restrict__ rowrec,
+                                                             unsigned* __restrict__ round_vis )
 {
 	if( PDL )
 		pdl_launch_dependents(); // the dependent grid may start once every forward warp has got this far (or exited)
@@ -130,11 +131,15 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 		                                             ( cwa.w & live[3] ) | ( cwb.x & live[4] ) | ( cwb.y & live[5] ) |
 		                                             ( cwb.z & live[6] ) | ( cwb.w & live[7] ) ) != 0u );
 
+		// the entries of this round that blended into at least one pixel (bit = list position in the round): the backward
+		// pass walks exactly these instead of testing every entry against its live masks again (round_visited)
+		unsigned vis_bits = 0u;
 #pragma unroll 1
 		while( ent )
 		{
 			const int k = __ffs( ent ) - 1;
 			ent &= ent - 1u;
+			const unsigned kbit = 1u << k;
 			const uint4 wa = *reinterpret_cast<const uint4*>( &sm.words[0][k][0] );
 			const uint4 wb = *reinterpret_cast<const uint4*>( &sm.words[0][k][4] );
 			const unsigned wd[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
@@ -156,6 +161,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 						continue;
 					if( COUNT )
 						nlive += count_visit( wl, lanebit, live, visit_hist, lane, g_visit_hist );
+					vis_bits |= kbit;
 					const float vx = ( j & 1 ) ? vx1 : vx0, avx = ( j & 1 ) ? avx1 : avx0, bvx = ( j & 1 ) ? bvx1 : bvx0;
 					const float vy = xsub( fpyr[j >> 1], q0.y );
 					// d2 = dot( v, inv_cov * v ), main.cpp:526 (inv_cov[0][1] == inv_cov[1][0] == b)
@@ -194,6 +200,7 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 						continue;
 					if( COUNT )
 						nlive += count_visit( wl, lanebit, live, visit_hist, lane, g_visit_hist );
+					vis_bits |= kbit;
 					const float vy = xsub( fpyr[j >> 1], q0.y );
 					const float alpha = relaxed_alpha( wl & lanebit, vy, q0.w, ( j & 1 ) ? bvx1 : bvx0, ( j & 1 ) ? axx1 : axx0 );
 					const float ta = __fmul_rn( T[j], alpha );
@@ -205,6 +212,8 @@ __global__ void __launch_bounds__( 32, MINB ) k_forward( Geometry g, const Splat
 				}
 			}
 		}
+		if( lane == 0 )
+			__stcg( round_vis + round_vis_index( start, tile_id, base ), vis_bits );
 		unsigned anylive = 0;
 #pragma unroll
 		for( int j = 0; j < 8; j++ )
@@ -266,7 +275,8 @@ static void launch_forward_as( dim3 grid, const Geometry& g, const Buffers& b, i
 	k_forward<MINB, COUNT, PDL, EXACT><<<grid, 32, 0, s>>>( g, b.rec, b.vals[sorted_buf], b.tile_range,
 	                                                       g.target_u8 ? reinterpret_cast<const float4*>( b.target8 ) : b.target, b.image,
 	                                                       b.cover, b.loss_partial, b.live_slots, b.staged_slots, b.state,
-	                                                       COUNT ? vh : 0, PDL ? b.tile_done : nullptr, b.rowtab, b.rowrec );
+	                                                       COUNT ? vh : 0, PDL ? b.tile_done : nullptr, b.rowtab, b.rowrec,
+	                                                       b.cover + 8 * (size_t)b.capacity );
 }
 template <int MINB, bool PDL>
 static void launch_forward_minb( dim3 grid, const Geometry& g, const Buffers& b, int sorted_buf, bool count_live,
