@@ -290,12 +290,14 @@ __global__ void __launch_bounds__( 32, MINB ) k_backward( Geometry g, const Spla
 				{
 					alpha = relaxed_alpha( wl & lanebit, vy, q0.w, bvx, avx );
 					wgt = __fmul_rn( T[j], alpha );          // == k_forward's T * alpha
-					Tn = __fsub_rn( T[j], wgt );             // == k_forward's transmittance chain
 				}
+				// every use of the old T in front of the new one (else the compiler keeps both and moves one at the end)
+				const float D = T[j] * fmaf( dLb[j], q1.w, fmaf( dLg[j], q1.z, dLr[j] * q1.y ) );
+				if( !EXACT )
+					Tn = __fsub_rn( T[j], wgt );             // == k_forward's transmittance chain
 				gc0 = fmaf( dLr[j], wgt, gc0 );
 				gc1 = fmaf( dLg[j], wgt, gc1 );
 				gc2 = fmaf( dLb[j], wgt, gc2 );
-				const float D = T[j] * fmaf( dLb[j], q1.w, fmaf( dLg[j], q1.z, dLr[j] * q1.y ) );
 				const float oma = xsub( 1.0f, alpha );
 				const bool dead = Tn < min_T;
 				float Qn = fmaf( -alpha, D, Q[j] );
