@@ -195,6 +195,9 @@ int gs2d_get_profile( gs2d_ctx* ctx, double sums_ms[6], long long* n_iters );
  * "GS2D_FWD_MINB" 32/24/20 and "GS2D_BWD_MINB" 24/20/16 = register caps of the blend kernels,
  * "GS2D_SLOTS" 2/1/0 = group rows (default: one key per (Gaussian, group of 4 tiles), sorted once per group) / slot
  * rows per (tile, index slice) / every (tile, Gaussian) pair through the place pass (same lists from all three),
+ * "GS2D_SCAN_FUSED" 1/0 = bucket totals + scan + chained block totals in one kernel (default) / three kernels,
+ * "GS2D_RT_LIST", "GS2D_BAND_LIST" 1/0 = a rank with a band walks lists of the Gaussians that reach it (default) / every
+ * Gaussian in every kernel (same results), "GS2D_K1_PROBE" = timing knock-outs of the binning kernel (results WRONG),
  * "GS2D_PDL" 1/0 = backward grid launched inside the forward grid's tail (default; needs the default register
  * caps) / the two grids serialised (same results), "GS2D_GRAPH" 1/0 = iterations replayed as a CUDA graph. */
 int gs2d_set_tuning( const char* name, int value );
