@@ -1222,7 +1222,11 @@ int launch_preprocess_and_bin( const Geometry& g, const Buffers& b, int* sorted_
 	const bool banded = g.band_ty0 > 0 || g.band_ty1 < g.tiles_y;
 	po.rt_count = po.n_over + 1;
 	po.rt_list = banded && b.rt_list && gs2d_tune( "GS2D_RT_LIST", 1 ) ? b.rt_list : nullptr;
-	const bool listed = banded && b.band_list && gs2d_tune( "GS2D_BAND_LIST", 1 );
+	// (worth it when at most a third of the Gaussians pass: with two ranks more than half do, and the filter pass costs
+	// what the fuller warps save - measured 0.105 vs 0.102 ms for one rank's band of 2; GS2D_BAND_LIST=2 forces it)
+	const int band_list = gs2d_tune( "GS2D_BAND_LIST", 1 );
+	const bool listed = banded && b.band_list && band_list &&
+	                    ( band_list > 1 || ( g.band_ty1 - g.band_ty0 ) * 3 <= g.tiles_y );
 	po.band_list = b.band_list;
 	po.band_count = po.n_over + 2;
 	cudaMemsetAsync( b.bucket_cnt, 0,
