@@ -137,3 +137,14 @@ struct PutArray
 	unsigned* base;
 	__device__ __forceinline__ void operator()( unsigned at, unsigned v ) const { base[at] = v; }
 };
+
+// ---- rounds of a tile's list (forward -> backward blend, gs2d_blend.cuh) -------------------------------------------
+// Where the forward pass leaves the 32-bit mask of a round's entries that blended into a pixel (k_forward -> k_backward):
+// one word per round of a tile. Rounds of tile t number (start_t >> 5) + t + round: floor((s + n)/32) >=
+// floor(s/32) + ceil(n/32) - 1, so the words of consecutive tiles never meet; capacity/32 + n_tiles + 1 words in all,
+// kept behind the coverage words (Buffers::cover). Here, not in gs2d_blend.cuh, so that the host test can see it.
+__device__ __forceinline__ size_t round_vis_index( unsigned start, unsigned tile_id, unsigned base )
+{
+	return (size_t)( start >> 5 ) + tile_id + ( ( base - start ) >> 5 );
+}
+

@@ -13,6 +13,7 @@
 // (entry, tile row) is solved once and scattered as bytes into the per-entry block words.
 #pragma once
 #include "gs2d_internal.cuh"
+#include "gs2d_bins.cuh" // round_vis_index
 
 // ( covered != 0 && !( t < exp_approx's cut-off ) ) ? value : 0 in three instructions (LOP3 with predicate output,
 // FSETP.GEU.AND on that predicate, FSEL): main.cpp:60 (`t < 0.000018...` -> 0) and the footprint / liveness test.
@@ -149,15 +150,6 @@ __device__ __forceinline__ bool pdl_wait_tile( const unsigned* flag, int lane )
 	}
 	ok = __shfl_sync( 0xffffffffu, ok, 0 ); // also orders the other lanes' loads after lane 0's acquire
 	return ok != 0u;
-}
-
-// Where the forward pass leaves the 32-bit mask of a round's entries that blended into a pixel (k_forward -> k_backward):
-// one word per round of a tile. Rounds of tile t number (start_t >> 5) + t + round: floor((s + n)/32) >=
-// floor(s/32) + ceil(n/32) - 1, so the words of consecutive tiles never meet; capacity/32 + n_tiles + 1 words in all,
-// kept behind the coverage words (Buffers::cover).
-__device__ __forceinline__ size_t round_vis_index( unsigned start, unsigned tile_id, unsigned base )
-{
-	return (size_t)( start >> 5 ) + tile_id + ( ( base - start ) >> 5 );
 }
 
 // WSTAGES = 1: the coverage words are solved in place (forward); 2: they are gathered like the records (backward)

@@ -140,6 +140,9 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 	return (long long)run;
 }
 
+// where the forward pass leaves the mask of round `round` of a tile whose list starts at `start` (round_vis_index)
+long long bins_round_vis_index( unsigned start, unsigned tile, unsigned round ) { return (long long)round_vis_index( start, tile, start + 32u * round ); }
+
 // the comparator networks on their own: sorts 16 keys in place (two sorted halves merged)
 void bins_sort16( unsigned* e )
 {

@@ -25,6 +25,8 @@ def bins(tmp_path_factory):
     L.bins_build.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
     L.bins_build.restype = C.c_longlong
     L.bins_sort16.argtypes = [C.c_void_p]
+    L.bins_round_vis_index.argtypes = [C.c_uint, C.c_uint, C.c_uint]
+    L.bins_round_vis_index.restype = C.c_longlong
     return L
 
 
@@ -89,3 +91,23 @@ def test_lists_are_complete_and_in_index_order(bins, tiles_x, tiles_y, n_splats,
             assert s == pos and e - s == len(truth[t]), (t, s, e, pos, len(truth[t]))  # lists are contiguous, in tile order
             assert list(out[s:e]) == sorted(truth[t]), t
             pos = e
+
+
+def test_round_mask_words_of_all_tiles_are_distinct_and_fit(bins):
+    """k_forward leaves one 32-bit mask per round (32 list entries) of a tile for k_backward at round_vis_index. The
+    tiles' lists are contiguous and of any length (0, 1, 31, 32, 33, ...): no two (tile, round) pairs may share a
+    word, and every index must lie below capacity / 32 + n_tiles + 1 (what gs2d_api.cu allocates behind the coverage
+    words)."""
+    rng = np.random.default_rng(3)
+    for trial in range(20):
+        n_tiles = int(rng.integers(1, 400))
+        lens = rng.choice([0, 0, 1, 2, 31, 32, 33, 63, 64, 65, 200], n_tiles) if trial % 2 else rng.integers(0, 300, n_tiles)
+        starts = np.concatenate([[0], np.cumsum(lens)[:-1]]) + int(rng.integers(0, 1000)) * (trial % 3 == 0)
+        total = int(starts[-1] + lens[-1])
+        seen = set()
+        for t in range(n_tiles):
+            for r in range((int(lens[t]) + 31) // 32):
+                i = bins.bins_round_vis_index(int(starts[t]), t, r)
+                assert i not in seen, (trial, t, r)
+                seen.add(i)
+                assert 0 <= i < total // 32 + n_tiles + 1, (trial, t, r, i, total)
