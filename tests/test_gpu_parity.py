@@ -332,7 +332,8 @@ def test_slot_binning_equals_the_triple_path():
              (700, 520, random_splats(rng, 700, 520, 1500, smin=100, smax=900, opacity=(0.1, 0.3)), None),
              (330, 250, random_splats(rng, 330, 250, 5000, smin=1, smax=30), None),   # 21 tiles per tile row
              (40, 400, random_splats(rng, 40, 400, 3000, smin=1, smax=20), None),     # 3 tiles per tile row
-             (700, 520, random_splats(rng, 700, 520, 6000, smin=2, smax=30), (1, 3))]
+             (700, 520, random_splats(rng, 700, 520, 6000, smin=2, smax=30), (1, 3)),
+             (330, 250, random_splats(rng, 330, 250, 5000, smin=1, smax=30), (1, 3))]  # band starts inside a group (tile 126)
     for W, H, splats, band in cases:
         out = []
         for slots in (0, 1, 2):
