@@ -19,7 +19,8 @@
 #define GS2D_TILE 16          // tile edge in pixels; one warp per tile, 8 pixels per lane (gs2d_blend.cuh)
 #define GS2D_BATCH 32         // list entries staged into shared memory per round
 #define GS2D_NPLANES 9
-#define GS2D_BUCKET_SLOTS 8   // direct slots per (tile, index slice) bucket, 16-bit entries (gs2d_binning.cu)
+#define GS2D_BUCKET_SLOTS 8   // GS2D_SLOTS=1: direct slots per (tile, index slice) bucket, 16-bit entries (gs2d_binning.cu);
+                              // the default binning keeps 16 32-bit keys per (group of 4 tiles, slice): GS2D_GROUP_SLOTS, gs2d_bins.cuh
 #define GS2D_LIVE_SLOTS 64    // spread of the live-pair counter atomics
 #define GS2D_FWD_MINB_DEFAULT 32 // resident warps per SM the forward blend is register-capped for (env GS2D_FWD_MINB)
 #define GS2D_BWD_MINB_DEFAULT 24 // same for the backward blend (env GS2D_BWD_MINB)
@@ -152,13 +153,16 @@ struct Buffers
 	unsigned* rowtab; // [n_total][GS2D_ROWTAB_STRIDE] packed row spans (k_row_table -> k_forward)
 	unsigned* rt_list; // [n_total] a banded rank: the splats k_row_table has to solve this iteration (k_preprocess appends)
 	unsigned* band_list; // [n_total] a banded rank: the splats that passed the band test (k_band_filter appends)
-	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word
-	unsigned short* bucket_slots; // [n_slices][nt_pad][GS2D_BUCKET_SLOTS] first arrivals of every bucket (slot binning)
+	unsigned short* bucket_cnt; // [n_slices][nt_pad] entries per (tile, index slice) bucket, 4 tiles per 64-bit word; behind
+	                            // them the counters of the group rows, the lists' lengths and the scan's scratch (gs2d_create)
+	unsigned short* bucket_slots; // group rows [nt_pad / 4][n_slices][16] 32-bit keys (default), or slot rows
+	                              // [n_slices][nt_pad][GS2D_BUCKET_SLOTS] of 16-bit indices (GS2D_SLOTS=1): same size
 	unsigned* bucket_off;       // [n_tiles_total * n_slices] exclusive scan of the counts in (tile, slice) order
 	unsigned* scan_sums;        // scratch of the scan
 	unsigned long long* triples; // [capacity] unordered (bucket, splat-in-slice, arrival rank) words, gs2d_binning.cu
 	unsigned* vals[2];          // vals[1]: the lists bucketed but unordered; vals[0]: ordered by splat index (final)
-	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward)
+	unsigned* cover;          // [capacity][8] exact coverage words of the staged list entries (forward -> backward), then
+	                          // [capacity / 32 + n_tiles + 8] round masks (round_vis_index)
 	unsigned long long capacity;
 	uint2* tile_range;        // [n_tiles_total]
 	float4* target;           // [n_images][H][W]
@@ -198,7 +202,8 @@ __device__ __forceinline__ float4 load_target( const Geometry& g, const float4* 
 	}
 	return target[pix];
 }
-// use_slots: slot binning unless the context has switched it off for now (gs2d_ctx::slot_binning) or GS2D_SLOTS=0
+// use_slots: group rows (GS2D_SLOTS=2, default) / slot rows (=1) unless the context has switched to the triple path for
+// now (gs2d_ctx::slot_binning: most arrivals overflow their rows) or GS2D_SLOTS=0
 // side: a second stream the row table kernel runs on, concurrently with the scan / place / rank kernels (fork and
 // join through ev_fork / ev_join; also inside a stream capture); nullptr: everything on s
 struct SideStream

@@ -445,9 +445,10 @@ def run_ours(args):
         kern["blend_overlapped_exact_mode"] = blend_entry(eb, FLOP_FWD + FLOP_BWD, **{"pass": "GS2D_EXACT=1, untimed"})
     kern["serialised_ms_per_step"] = {"ms": sep_ms}
     if prof["sort"] > 0:
-        # k_scan_* + k_place + k_rank with slot binning (gs2d_binning.cu): per bucket (3.4 entries) the 16-byte slot row,
-        # the 2-byte counter twice (scan, k_rank), the 4-byte offset written and read = 30 B, i.e. 9 B per list entry,
-        # + 4 B per entry written in index order. k_row_table runs beside these kernels on a second stream.
+        # k_group_scan + k_place + k_rank_groups with group rows (gs2d_binning.cu): per (group of 4 tiles, index slice)
+        # pair (13 list entries) the 64-byte row and the 4-byte counter read twice (scan, rank) and four 4-byte offsets
+        # written and read = ~9 B per list entry, + 4 B per entry written in index order. k_row_table runs beside these
+        # kernels on a second stream.
         b = keys_per_it / world * BIN_BYTES_PER_KEY
         a = b / (prof["sort"] * 1e-3) / 1e9
         kern["place_rank"] = {"ms": prof["sort"], "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s",
