@@ -83,9 +83,9 @@ __device__ __forceinline__ void reduce_group( const float ( *stg )[STAGE_STRIDE]
 	__syncwarp();
 	const unsigned half = (unsigned)lane >> 4, slot = ( (unsigned)lane >> 3 ) & 1u, val = (unsigned)lane & 7u;
 	const float* src = &stg[slot][half * 128u + val];
-	float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+	float s0 = src[0], s1 = src[8], s2 = src[16], s3 = src[24]; // (not 0 + x: the compiler keeps that add, -0 + 0 is +0)
 #pragma unroll
-	for( int l = 0; l < 16; l += 4 )
+	for( int l = 4; l < 16; l += 4 )
 	{
 		s0 += src[l * 8];
 		s1 += src[l * 8 + 8];
