@@ -241,7 +241,7 @@ struct PeerPtrs
 	float* params[GS2D_MAX_RANKS];
 	int n_ranks, rank;
 	int sum_all; // 1: sum the gradients of all ranks; 0: this rank's gradients are already the total
-	// Sparse exchange (GS2D_PEER_SPARSE, default on). A Gaussian reaches 1.15 of 8 bands on average, so most of what the
+	// Sparse exchange (GS2D_PEER_SPARSE; the default from three ranks on, dense at two). A Gaussian reaches 1.15 of 8 bands on average, so most of what the
 	// dense exchange moves is zeros (gradients) or parameters the receiver never looks at:
 	//   touch[r] : rank r's bitmap of the quads (4 consecutive Gaussians) that passed its band test in k_preprocess this
 	//              iteration, i.e. that CAN hold a non-zero gradient on r; the owner of a quad reads the gradient quads

@@ -172,8 +172,8 @@ int gs2d_comm_mode( const gs2d_ctx* ctx, int* n_ranks, int* peer_memory );
 /* NVLink payload of the peer-memory exchange since the context was created or the counters were last reset: bytes of
  * gradient quads this rank read out of its peers' memory and bytes of parameter quads it wrote into it (counted by the
  * exchange kernel itself; 0 on one GPU and on the NCCL path). *sparse = 1 when the exchange skips what a rank cannot
- * have touched / will not look at (default; environment variable GS2D_PEER_SPARSE=0: every quad to and from every
- * rank). Waits for the stream. Any pointer may be NULL. */
+ * have touched / will not look at (the default from three ranks on; environment variable GS2D_PEER_SPARSE=0 / 1: every
+ * quad to and from every rank / sparse also at two ranks). Waits for the stream. Any pointer may be NULL. */
 int gs2d_comm_traffic( gs2d_ctx* ctx, uint64_t* bytes_read, uint64_t* bytes_written, int* sparse, int reset );
 /* Band sharding WITHOUT a communicator (host-side tests on one GPU: render bands separately and add them up). */
 int gs2d_set_band( gs2d_ctx* ctx, int rank, int n_ranks );
