@@ -18,8 +18,11 @@ extern "C" {
 // (consecutive ids, may cross group boundaries). slice_size: splat = slice * slice_size + local.
 // Window [tile_lo_w, tile_hi_w) as for a rank's band. Outputs: out_list (capacity cap), tile_range (2 per tile).
 // Returns the total number of list entries, or -1 if cap is too small.
+// fused != 0: offsets the way k_group_scan lays them out (blocks of 256 pairs = 1024 consecutive buckets from the first
+// bucket of the window's first GROUP, block-local offsets + sums[block]); else the plain scan of the three kernels.
 long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, int tile_hi_w, const int* arrivals,
-                      long long n_arr, unsigned* out_list, long long cap, unsigned* tile_range, long long* n_overflow )
+                      long long n_arr, unsigned* out_list, long long cap, unsigned* tile_range, long long* n_overflow,
+                      int fused )
 {
 	const unsigned ns = (unsigned)n_slices;
 	const int nt_pad = ( n_tiles + 3 ) & ~3;
@@ -73,13 +76,60 @@ long long bins_build( int n_tiles, int n_slices, int slice_size, int tile_lo_w, 
 		}
 	}
 	// ---- exclusive scan over [lo, hi], one item more than buckets
-	std::vector<unsigned> offset( (size_t)n_tiles * ns + 2, 0u );
+	std::vector<unsigned> offset( (size_t)( n_tiles + 4 ) * ns + 1026, 0u );
 	unsigned run = 0;
-	for( unsigned i = lo; i <= hi; i++ )
+	if( !fused )
 	{
-		offset[i] = run;
-		if( i < hi )
-			run += tot16[i];
+		for( unsigned i = lo; i <= hi; i++ )
+		{
+			offset[i] = run;
+			if( i < hi )
+				run += tot16[i];
+		}
+	}
+	else
+	{
+		// k_group_scan: thread t of block blk is pair blk * 256 + t of the window; its four counts go to items
+		// ( t / ns * 4 + f ) * ns + t % ns of the block; items are scanned in order, offsets stay block-local
+		const unsigned base = grp_lo * 4u * ns, n_pairs_w = ( grp_hi - grp_lo ) * ns, n_off = hi + 1u;
+		const unsigned n_blocks = ( hi - base + 1u + 1023u ) / 1024u;
+		std::vector<unsigned> local( offset.size(), 0u ), sums( n_blocks + 1, 0u );
+		for( unsigned blk = 0; blk < n_blocks; blk++ )
+		{
+			unsigned short cnt_s[1024];
+			for( unsigned t = 0; t < 256u; t++ )
+			{
+				const unsigned p = blk * 256u + t;
+				const bool valid = p < n_pairs_w;
+				const size_t pair = (size_t)grp_lo * ns + ( valid ? p : 0u );
+				const unsigned grp = (unsigned)( pair / ns );
+				const unsigned c_raw = valid ? grp_cnt[pair] : 0u, c = min( c_raw, (unsigned)GS2D_GROUP_SLOTS );
+				unsigned n[4];
+				group_counts( &rows[pair * GS2D_GROUP_SLOTS], c, c, n );
+				if( c_raw > (unsigned)GS2D_GROUP_SLOTS )
+					for( unsigned f = 0; f < 4u; f++ )
+						n[f] += (unsigned)( ovf64[pair] >> ( 16u * f ) ) & 0xffffu;
+				const unsigned g_local = t / ns, s_local = t - g_local * ns;
+				for( unsigned f = 0; f < 4u; f++ )
+				{
+					const unsigned tile = grp * 4u + f;
+					const bool in = valid && tile >= (unsigned)tile_lo_w && tile < (unsigned)tile_hi_w;
+					cnt_s[( g_local * 4u + f ) * ns + s_local] = (unsigned short)( in ? n[f] : 0u );
+				}
+			}
+			unsigned r = 0;
+			for( unsigned i = 0; i < 1024u; i++ )
+			{
+				if( base + blk * 1024u + i < n_off )
+					local[base + blk * 1024u + i] = r;
+				r += cnt_s[i];
+			}
+			sums[blk] = run;
+			run += r;
+		}
+		// what the consumers compute: bucket_offset( offset, sums, bucket, base )
+		for( unsigned i = lo; i <= hi; i++ )
+			offset[i] = local[i] + sums[( i - base ) / 1024u];
 	}
 	if( (long long)run > cap )
 		return -1;

@@ -1,6 +1,7 @@
 """CPU tests of the product's group-row binning (no GPU): 2dgaussiansplatting_b200/csrc/gs2d_bins.cuh - the very header
 gs2d_binning.cu includes for its default path (GS2D_SLOTS=2) - is compiled for the host by tests/bins_host.cpp, which
-walks it through the kernels' sequence (emission in arbitrary arrival order -> totals -> scan -> overflow placement ->
+walks it through the kernels' sequence (emission in arbitrary arrival order -> totals -> scan, plain and in the block
+layout of the fused kernel -> overflow placement ->
 one sort per (group of 4 tiles, index slice) and the deal to the tiles' lists). Every tile's list must hold exactly the
 splats whose tile rows cover it, in splat-index order (== the reference's blend order, main.cpp:419), whatever the
 arrival order, for tile rows that straddle groups, groups that straddle tile rows (tiles_x not a multiple of 4), rows
@@ -22,7 +23,7 @@ def bins(tmp_path_factory):
     subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", os.path.join(HERE, "bins_host.cpp"), "-o", so],
                    check=True)
     L = C.CDLL(so)
-    L.bins_build.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
+    L.bins_build.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p, C.c_int]
     L.bins_build.restype = C.c_longlong
     L.bins_sort16.argtypes = [C.c_void_p]
     L.bins_round_vis_index.argtypes = [C.c_uint, C.c_uint, C.c_uint]
@@ -79,8 +80,9 @@ def test_lists_are_complete_and_in_index_order(bins, tiles_x, tiles_y, n_splats,
         out = np.full(cap, 0xFFFFFFFF, np.uint32)
         tr = np.full((n_tiles, 2), 0xFFFFFFFF, np.uint32)
         n_over = C.c_longlong(0)
+        # trial 0: offsets by the plain scan (k_group_count + k_scan_*), then by k_group_scan's block layout
         total = bins.bins_build(n_tiles, n_slices, slice_size, row_lo * tiles_x, row_hi * tiles_x, a.ctypes.data, len(a),
-                                out.ctypes.data, cap, tr.ctypes.data, C.byref(n_over))
+                                out.ctypes.data, cap, tr.ctypes.data, C.byref(n_over), int(trial > 0))
         want_total = sum(len(truth[t]) for t in range(row_lo * tiles_x, row_hi * tiles_x))
         assert total == want_total
         if (tiles_x, n_splats) == (8, 4000):
